@@ -1,0 +1,236 @@
+"""ctypes binding of include/ctr_engine.h.  No fallback: if libctr_b200.so is missing or a
+call fails, this raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libctr_b200.so")
+
+CTR_OK = 0
+ERR_NAMES = {-1: "CTR_ERR_INVALID", -2: "CTR_ERR_CUDA", -3: "CTR_ERR_IO", -4: "CTR_ERR_STATE",
+             -5: "CTR_ERR_TIMEOUT", -6: "CTR_ERR_CAPACITY"}
+CTR_MAX_DEVICES, CTR_MAX_HIDDEN = 8, 4
+TABLES_REPLICATED, TABLES_ROW_SHARDED = 0, 1
+
+# every symbol include/ctr_engine.h declares (tests check the library exports exactly these)
+EXPORTS = ["ctr_engine_create", "ctr_engine_destroy", "ctr_engine_load_weights", "ctr_engine_model_info",
+           "ctr_predict_async", "ctr_wait", "ctr_predict", "ctr_alloc_pinned", "ctr_free_pinned",
+           "ctr_score_device", "ctr_partition_bounds", "ctr_last_error", "ctr_abi_version",
+           "ctr_engine_launch_count", "ctr_engine_set_timing", "ctr_engine_stage_ms", "ctr_debug_read_rows",
+           "ctr_debug_gemm", "ctr_debug_gather"]
+
+
+class CtrConfig(C.Structure):
+    _fields_ = [("struct_size", C.c_int32), ("n_devices", C.c_int32), ("device_ids", C.c_int32 * CTR_MAX_DEVICES),
+                ("max_candidates", C.c_int32), ("workers_per_device", C.c_int32), ("shard_mode", C.c_int32),
+                ("reserved", C.c_int32 * 8)]
+
+
+class CtrModelInfo(C.Structure):
+    _fields_ = [("model_kind", C.c_int32), ("num_fields", C.c_int32), ("emb_dim", C.c_int32), ("id_mode", C.c_int32),
+                ("table_dtype", C.c_int32), ("n_hidden", C.c_int32), ("hidden", C.c_int32 * CTR_MAX_HIDDEN),
+                ("n_cross", C.c_int32), ("d_padded", C.c_int32), ("num_rows", C.c_int64),
+                ("table_bytes_per_device", C.c_int64)]
+
+
+CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int32)
+
+
+class CtrError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__("%s (%d): %s" % (ERR_NAMES.get(code, "CTR_ERR"), code, msg))
+        self.code = code
+
+
+_lib: Optional[C.CDLL] = None
+
+
+def load_library() -> C.CDLL:
+    """Loads libctr_b200.so.  Raises if it has not been built: the engine has no other path."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError("%s is missing: build it with __graft_entry__.build() "
+                           "(nvcc, sm_100a). There is no CPU or PyTorch fallback." % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+    lib.ctr_engine_create.argtypes = [C.POINTER(CtrConfig), C.POINTER(vp)]
+    lib.ctr_engine_destroy.argtypes = [vp]
+    lib.ctr_engine_load_weights.argtypes = [vp, C.c_char_p]
+    lib.ctr_engine_model_info.argtypes = [vp, C.POINTER(CtrModelInfo)]
+    lib.ctr_predict_async.argtypes = [vp, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
+    lib.ctr_wait.argtypes = [vp, i64, i32]
+    lib.ctr_predict.argtypes = [vp, vp, vp, i64, vp]
+    lib.ctr_alloc_pinned.argtypes = [vp, i64, C.POINTER(vp)]
+    lib.ctr_free_pinned.argtypes = [vp, vp]
+    lib.ctr_score_device.argtypes = [vp, i32, vp, vp, i64, vp, vp]
+    lib.ctr_partition_bounds.argtypes = [i64, i32, vp, vp]
+    lib.ctr_last_error.restype = C.c_char_p
+    lib.ctr_engine_launch_count.argtypes = [vp]
+    lib.ctr_engine_launch_count.restype = i64
+    lib.ctr_engine_set_timing.argtypes = [vp, i32]
+    lib.ctr_engine_stage_ms.argtypes = [vp, i32, i32]
+    lib.ctr_engine_stage_ms.restype = C.c_double
+    lib.ctr_debug_read_rows.argtypes = [vp, i32, vp, i64, vp, vp]
+    lib.ctr_debug_gemm.argtypes = [vp, i32, vp, vp, vp, i32, i32, i32, i32, vp]
+    lib.ctr_debug_gather.argtypes = [vp, i32, vp, vp, i64, vp, vp]
+    _lib = lib
+    return lib
+
+
+def _check(rc: int) -> None:
+    if rc != CTR_OK:
+        raise CtrError(rc, (load_library().ctr_last_error() or b"").decode("utf-8", "replace"))
+
+
+def partition_bounds(n: int, part_num: int):
+    """DCNClient.java:46-55 through the C ABI."""
+    b = np.zeros(max(part_num, 1), np.int64)
+    e = np.zeros(max(part_num, 1), np.int64)
+    _check(load_library().ctr_partition_bounds(n, part_num, b.ctypes.data, e.ctypes.data))
+    return list(zip(b.tolist(), e.tolist()))
+
+
+class PinnedBuffer:
+    """numpy view over memory from ctr_alloc_pinned (the zero-copy packer's slab)."""
+
+    def __init__(self, engine: "Engine", shape, dtype):
+        self.engine = engine
+        dtype = np.dtype(dtype)
+        nbytes = int(np.prod(shape)) * dtype.itemsize
+        p = C.c_void_p()
+        _check(engine.lib.ctr_alloc_pinned(engine.handle, max(nbytes, 16), C.byref(p)))
+        self.ptr = p.value
+        buf = (C.c_char * max(nbytes, 16)).from_address(self.ptr)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self):
+        if self.ptr is not None and self.engine.handle:
+            self.array = None
+            _check(self.engine.lib.ctr_free_pinned(self.engine.handle, self.ptr))
+        self.ptr = None
+
+
+class Engine:
+    """One engine = the reference's channel list (getChannels, DCNClient.java:118-125): one
+    "channel" per GPU."""
+
+    def __init__(self, device_ids=(0,), max_candidates: int = 16384, workers_per_device: int = 0,
+                 shard_mode: int = TABLES_REPLICATED):
+        self.lib = load_library()
+        cfg = CtrConfig()
+        cfg.struct_size = C.sizeof(CtrConfig)
+        cfg.n_devices = len(device_ids)
+        for i, d in enumerate(device_ids):
+            cfg.device_ids[i] = d
+        cfg.max_candidates = max_candidates
+        cfg.workers_per_device = workers_per_device
+        cfg.shard_mode = shard_mode
+        h = C.c_void_p()
+        _check(self.lib.ctr_engine_create(C.byref(cfg), C.byref(h)))
+        self.handle = h.value
+        self.n_devices = len(device_ids)
+        self.num_fields = None
+        self._keep = {}
+
+    def close(self):
+        if self.handle:
+            self.lib.ctr_engine_destroy(self.handle)
+            self.handle = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def load_weights(self, path: str) -> CtrModelInfo:
+        _check(self.lib.ctr_engine_load_weights(self.handle, path.encode()))
+        info = CtrModelInfo()
+        _check(self.lib.ctr_engine_model_info(self.handle, C.byref(info)))
+        self.num_fields = info.num_fields
+        self.info = info
+        return info
+
+    # -- host request path -------------------------------------------------------------
+    def _check_inputs(self, ids, wts):
+        ids = np.asarray(ids)
+        wts = np.asarray(wts)
+        if ids.dtype != np.int64 or wts.dtype != np.float32:
+            raise TypeError("ids must be int64 and wts float32 (the reference's DT_INT64 / DT_FLOAT tensors)")
+        if not (ids.flags.c_contiguous and wts.flags.c_contiguous):
+            raise ValueError("ids / wts must be C-contiguous")
+        if ids.size != wts.size or ids.size % self.num_fields:
+            raise ValueError("ids / wts need n_cand * %d elements each" % self.num_fields)
+        return ids, wts, ids.size // self.num_fields
+
+    def predict_async(self, ids, wts, out: Optional[np.ndarray] = None):
+        ids, wts, n = self._check_inputs(ids, wts)
+        if out is None:
+            out = np.empty(n, np.float32)
+        t = C.c_int64()
+        _check(self.lib.ctr_predict_async(self.handle, ids.ctypes.data, wts.ctypes.data, n, out.ctypes.data,
+                                          None, None, C.byref(t)))
+        self._keep[t.value] = (ids, wts, out)
+        return t.value, out
+
+    def wait(self, ticket: int, timeout_ms: int = -1) -> np.ndarray:
+        rc = self.lib.ctr_wait(self.handle, ticket, timeout_ms)
+        if rc == -5:
+            raise CtrError(rc, "timed out")
+        kept = self._keep.pop(ticket, None)
+        _check(rc)
+        return kept[2] if kept else None
+
+    def predict(self, ids, wts, out: Optional[np.ndarray] = None) -> np.ndarray:
+        t, out = self.predict_async(ids, wts, out)
+        return self.wait(t)
+
+    def pinned(self, shape, dtype) -> PinnedBuffer:
+        return PinnedBuffer(self, shape, dtype)
+
+    # -- device-resident path ----------------------------------------------------------
+    def score_device(self, d_ids: int, d_wts: int, n_cand: int, d_scores: int, stream: int = 0, device_index: int = 0):
+        """Raw device pointers (ints) and a cudaStream_t handle (0 = engine stream, blocking)."""
+        _check(self.lib.ctr_score_device(self.handle, device_index, d_ids, d_wts, n_cand, d_scores, stream or None))
+
+    def launch_count(self) -> int:
+        return int(self.lib.ctr_engine_launch_count(self.handle))
+
+    def set_timing(self, on: bool):
+        _check(self.lib.ctr_engine_set_timing(self.handle, 1 if on else 0))
+
+    def stage_ms(self, stage: int, device_index: int = 0) -> float:
+        return float(self.lib.ctr_engine_stage_ms(self.handle, device_index, stage))
+
+    def read_rows(self, rows, device_index: int = 0):
+        rows = np.ascontiguousarray(rows, np.int64)
+        emb = np.empty((rows.size, 16), np.float32)
+        w1 = np.empty(rows.size, np.float32)
+        _check(self.lib.ctr_debug_read_rows(self.handle, device_index, rows.ctypes.data, rows.size,
+                                            emb.ctypes.data, w1.ctypes.data))
+        return emb, w1
+
+    def debug_gemm(self, A, W, bias, device_index: int = 0) -> np.ndarray:
+        """relu(half(A) @ half(W).T + bias) through the tcgen05 kernel alone; A [M,K], W [N,K]."""
+        A = np.ascontiguousarray(A, np.float32); W = np.ascontiguousarray(W, np.float32)
+        bias = np.ascontiguousarray(bias, np.float32)
+        M, K = A.shape; N = W.shape[0]
+        out = np.empty((M, N), np.float32)
+        _check(self.lib.ctr_debug_gemm(self.handle, device_index, A.ctypes.data, W.ctypes.data, bias.ctypes.data,
+                                       M, N, K, 1, out.ctypes.data))
+        return out
+
+    def debug_gather(self, ids, wts, device_index: int = 0):
+        ids, wts, n = self._check_inputs(ids, wts)
+        d = self.num_fields * 16
+        x = np.zeros((n, d), np.float32); wide = np.zeros(n, np.float32)
+        _check(self.lib.ctr_debug_gather(self.handle, device_index, ids.ctypes.data, wts.ctypes.data, n,
+                                         x.ctypes.data, wide.ctypes.data))
+        return x, wide

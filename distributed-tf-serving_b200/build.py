@@ -1,0 +1,53 @@
+"""Builds libctr_b200.so (CUDA kernels + C ABI + host runtime) for sm_100a, in-tree."""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libctr_b200.so")
+HOST_DEMO = os.path.join(HERE, "dcn_client_host")
+SOURCES = ["engine.cu", "common.cuh", "gather.cuh", "gemm_f16.cuh", os.path.join("..", "..", "include", "ctr_engine.h")]
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC,-Wall,-pthread", "-shared"]
+
+
+def _nvcc() -> str:
+    nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(nvcc):
+        raise RuntimeError("nvcc not found: the engine has no prebuilt or CPU path")
+    return nvcc
+
+
+def _stale(target: str, deps) -> bool:
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+
+
+def build_library(force: bool = False, verbose: bool = False) -> str:
+    deps = [os.path.join(CSRC, s) for s in SOURCES]
+    if force or _stale(LIB, deps):
+        cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB, os.path.join(CSRC, "engine.cu")]
+        subprocess.check_call(cmd, cwd=CSRC)
+    return LIB
+
+
+def build_host_demo(force: bool = False) -> str:
+    """C++ host mirror of DCNClient.main (6 closed-loop driver threads over the C ABI)."""
+    src = os.path.join(CSRC, "dcn_client_host.cpp")
+    if not os.path.exists(src):
+        return ""
+    if force or _stale(HOST_DEMO, [src, os.path.join(CSRC, "..", "..", "include", "ctr_engine.h")]):
+        cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+        subprocess.check_call([cxx, "-O2", "-std=c++17", "-pthread", "-o", HOST_DEMO, src, "-ldl"], cwd=CSRC)
+    return HOST_DEMO
+
+
+def build_all(force: bool = False) -> None:
+    build_library(force)
+    build_host_demo(force)

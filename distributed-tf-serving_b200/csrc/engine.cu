@@ -1,0 +1,1167 @@
+// engine.cu -- host runtime + C ABI of the B200-native CTR scoring engine.
+//
+// What this file replaces in the reference (DC = src/main/java/tensorflow/serving/DCNClient.java):
+//   processARequest  DC:137-203  -> ctr_predict_async / ctr_wait: split, fan-out to devices, ordered merge
+//   partitionList    DC:46-55    -> split_bounds(): range = n / parts, remainder to the last part
+//   sendRequest      DC:91-115   -> Worker::run_task(): pinned staging + cudaMemcpyAsync instead of protobuf
+//                                   marshalling, then the kernels instead of the TF-Serving RPC
+//   threadPool       DC:42       -> worker threads, one CUDA stream each, per device
+//   getChannels      DC:118-125  -> ctr_engine_create (one "channel" per GPU)
+// The model arithmetic the reference delegates to an external SavedModel is the CUDA path in
+// gather.cuh / gemm_f16.cuh.  There is no CPU fallback anywhere.
+#include "../../include/ctr_engine.h"
+#include "common.cuh"
+#include "gather.cuh"
+#include "gemm_f16.cuh"
+
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+namespace {
+
+using namespace ctr;
+
+thread_local std::string g_last_error;
+
+int32_t fail(int32_t code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                   \
+    do {                                                                                                 \
+        cudaError_t _e = (expr);                                                                         \
+        if (_e != cudaSuccess) {                                                                         \
+            (void)cudaGetLastError();                                                                    \
+            return fail(CTR_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));               \
+        }                                                                                                \
+    } while (0)
+
+inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// ------------------------------------------------------------------ driver entry point for tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// half matrix [rows, cols] with leading dimension ld (elements), box {64, box_rows}, 128-byte swizzle
+int32_t make_map_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * sizeof(__half)};
+    cuuint32_t box[2] = {(cuuint32_t)kBK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    return CTR_OK;
+}
+
+// ------------------------------------------------------------------ weight file (format: DESIGN.md)
+constexpr char kMagic[8] = {'C', 'T', 'R', 'W', '0', '0', '0', '1'};
+constexpr size_t kHeaderBytes = 128;
+constexpr uint64_t kTagE = 1, kTagW1 = 2;
+
+struct ModelDesc {
+    int32_t kind = 0, F = 0, K = 0, id_mode = 0, table_dtype = 0, table_mode = 0, n_hidden = 0;
+    int32_t hidden[CTR_MAX_HIDDEN] = {0, 0, 0, 0};
+    int32_t n_cross = 0;
+    int64_t V = 0;
+    uint64_t seed = 0;
+    float scale_e = 0, scale_w1 = 0;
+    int d() const { return F * K; }
+    int d_pad() const { return round_up(F * K, 128); }
+    int head_in() const { return kind == CTR_MODEL_LR ? 0 : (n_hidden ? hidden[n_hidden - 1] : 0) + (kind == CTR_MODEL_DCN_V2 ? d() : 0); }
+};
+
+struct HostWeights {
+    ModelDesc m;
+    std::vector<float> blob;        // everything after the header
+    size_t off_b0 = 0, off_w1 = 0, off_emb = 0, off_wout = 0, off_bout = 0;
+    std::vector<size_t> off_mlp_w, off_mlp_b, off_cross_w, off_cross_b;
+};
+
+int32_t read_weight_file(const char* path, HostWeights* hw) {
+    FILE* f = fopen(path, "rb");
+    if (!f) return fail(CTR_ERR_IO, std::string("cannot open weight file ") + path);
+    unsigned char hdr[kHeaderBytes];
+    if (fread(hdr, 1, kHeaderBytes, f) != kHeaderBytes || memcmp(hdr, kMagic, 8) != 0) {
+        fclose(f);
+        return fail(CTR_ERR_IO, "weight file: bad header / magic");
+    }
+    ModelDesc& m = hw->m;
+    int32_t iv[12];
+    memcpy(iv, hdr + 8, sizeof(iv));
+    m.kind = iv[0]; m.F = iv[1]; m.K = iv[2]; m.id_mode = iv[3]; m.table_dtype = iv[4]; m.table_mode = iv[5]; m.n_hidden = iv[6];
+    for (int i = 0; i < CTR_MAX_HIDDEN; ++i) m.hidden[i] = iv[7 + i];
+    m.n_cross = iv[11];
+    memcpy(&m.V, hdr + 56, 8);
+    memcpy(&m.seed, hdr + 64, 8);
+    memcpy(&m.scale_e, hdr + 72, 4);
+    memcpy(&m.scale_w1, hdr + 76, 4);
+
+    auto bad = [&](const char* why) { fclose(f); return fail(CTR_ERR_IO, std::string("weight file: ") + why); };
+    if (m.kind < 0 || m.kind > 3) return bad("unknown model kind");
+    if (m.K != kEmbDim) return bad("embedding dim must be 16");
+    if (m.F < 1 || m.F > CTR_MAX_FIELDS) return bad("field count out of range (1..48)");
+    if (m.V < 1) return bad("row count must be positive");
+    if (m.id_mode == CTR_ID_HASHED && (m.V & (m.V - 1))) return bad("hashed tables need a power-of-two row count");
+    if (m.n_hidden < 0 || m.n_hidden > CTR_MAX_HIDDEN) return bad("too many hidden layers");
+    if (m.kind != CTR_MODEL_LR && m.n_hidden < 1) return bad("tower needs at least one hidden layer");
+    for (int i = 0; i < m.n_hidden; ++i)
+        if (m.hidden[i] < 8 || m.hidden[i] % 8) return bad("hidden sizes must be positive multiples of 8");
+    if (m.kind != CTR_MODEL_DCN_V2) m.n_cross = 0;
+    if (m.n_cross < 0 || m.n_cross > 8) return bad("cross layer count out of range");
+
+    size_t n = 1;
+    hw->off_b0 = 0;
+    if (m.table_mode == 0) { hw->off_w1 = n; n += (size_t)m.V; hw->off_emb = n; n += (size_t)m.V * m.K; }
+    if (m.kind != CTR_MODEL_LR) {
+        int fan_in = m.d();
+        for (int l = 0; l < m.n_hidden; ++l) {
+            hw->off_mlp_w.push_back(n); n += (size_t)m.hidden[l] * fan_in;
+            hw->off_mlp_b.push_back(n); n += (size_t)m.hidden[l];
+            fan_in = m.hidden[l];
+        }
+        for (int l = 0; l < m.n_cross; ++l) {
+            hw->off_cross_w.push_back(n); n += (size_t)m.d() * m.d();
+            hw->off_cross_b.push_back(n); n += (size_t)m.d();
+        }
+        hw->off_wout = n; n += (size_t)m.head_in();
+        hw->off_bout = n; n += 1;
+    }
+    hw->blob.resize(n);
+    size_t got = fread(hw->blob.data(), sizeof(float), n, f);
+    unsigned char extra;
+    bool trailing = fread(&extra, 1, 1, f) == 1;
+    fclose(f);
+    if (got != n) return fail(CTR_ERR_IO, "weight file: truncated tensor data");
+    if (trailing) return fail(CTR_ERR_IO, "weight file: trailing bytes after the last tensor");
+    return CTR_OK;
+}
+
+// ------------------------------------------------------------------ per-device model state
+struct GemmLayer {
+    int N = 0, Npad = 0, Kpad = 0, BN = 0;
+    __half* W = nullptr;      // [Npad, Kpad]
+    float* bias = nullptr;    // [Npad]
+    CUtensorMap map_w;
+};
+
+struct DeviceModel {
+    int dev = -1;
+    int num_sms = 148;
+    uint8_t* table = nullptr;          // packed rows (local shard when row-sharded)
+    uint64_t table_rows_local = 0;
+    size_t table_bytes = 0;
+    std::vector<GemmLayer> mlp, cross;
+    float* w_out_h = nullptr;          // [Npad of last hidden] head weights for the hidden part
+    float* w_out_x = nullptr;          // [d_pad] head weights for x_L (DCN-v2)
+    float b0 = 0.f, b_out = 0.f;
+    bool loaded = false;
+};
+
+struct GemmOp {
+    int layer_kind;   // 0 mlp, 1 cross
+    int layer;
+    int epi;
+    int a_buf, out_buf, xl_buf;    // buffer ids: 0 X, 1 H0, 2 H1, 3 XL0, 4 XL1
+    CUtensorMap map_a;
+};
+
+// One stream with its private activation buffers ("slot"): everything a shard needs on the device.
+struct Slot {
+    int dev = -1;
+    cudaStream_t stream = nullptr;
+    bool owns_stream = true;
+    int64_t cap = 0;           // candidate capacity of the id/weight/score buffers
+    int act_rows = 0;          // rows of the activation buffers (chunk size)
+    int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;
+    float* d_wide = nullptr; float* d_extra = nullptr; int32_t* d_err = nullptr;
+    __half* buf[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    int ld[5] = {0, 0, 0, 0, 0};
+    std::vector<GemmOp> ops;
+    // pinned staging for pageable callers
+    int64_t* h_ids = nullptr; float* h_wts = nullptr; float* h_scores = nullptr; int32_t* h_err = nullptr;
+    // timing
+    cudaEvent_t ev[16]; bool ev_ok = false; int n_ev = 0; int ev_stage[16]; bool time_this = false;
+    cudaEvent_t join_ev = nullptr;
+    float stage_ms[16]; int n_stage = 0; float total_ms = -1.f;
+};
+
+struct Request {
+    std::atomic<int> pending{0};
+    std::atomic<int> status{CTR_OK};
+    std::string error;
+    std::mutex m;
+    std::condition_variable cv;
+    bool done = false;
+    ctr_callback cb = nullptr;
+    void* user = nullptr;
+    ctr_ticket ticket = 0;
+};
+
+struct Task {
+    std::shared_ptr<Request> req;
+    const int64_t* ids; const float* wts; int64_t n; float* scores;
+    bool stop = false;
+};
+
+struct DeviceCtx {
+    DeviceModel model;
+    std::vector<std::unique_ptr<Slot>> worker_slots;
+    std::vector<std::unique_ptr<Slot>> dev_slots;     // for ctr_score_device
+    std::mutex dev_mu;                                // serialises ctr_score_device enqueues per device
+    cudaStream_t main_stream = nullptr;
+    cudaEvent_t fork_ev = nullptr;
+    std::deque<Task> queue;
+    std::mutex q_mu;
+    std::condition_variable q_cv;
+    std::vector<std::thread> threads;
+};
+
+}  // namespace
+
+struct ctr_engine {
+    ctr_config cfg;
+    ModelDesc m;
+    bool loaded = false;
+    bool timing = false;
+    int chunk_rows = 16384;
+    std::vector<std::unique_ptr<DeviceCtx>> devs;
+    std::mutex t_mu;
+    std::unordered_map<ctr_ticket, std::shared_ptr<Request>> tickets;
+    std::atomic<int64_t> next_ticket{1};
+    std::atomic<int64_t> launches{0};
+    std::mutex pin_mu;
+    std::map<uintptr_t, size_t> pinned;     // base -> bytes (buffers from ctr_alloc_pinned)
+    std::atomic<bool> shutting_down{false};
+    uint8_t* shard_base[CTR_MAX_DEVICES] = {nullptr};   // row-sharded tables: every device's shard
+};
+
+namespace {
+
+// DC:46-55 applied to candidates
+void split_bounds(int64_t n, int parts, int64_t* b, int64_t* e) {
+    const int64_t range = n / parts;
+    for (int i = 0; i < parts - 1; ++i) { b[i] = i * range; e[i] = (i + 1) * range; }
+    b[parts - 1] = (int64_t)(parts - 1) * range;
+    e[parts - 1] = n;
+}
+
+bool is_pinned(ctr_engine* e, const void* p, size_t bytes) {
+    std::lock_guard<std::mutex> lk(e->pin_mu);
+    if (e->pinned.empty()) return false;
+    auto it = e->pinned.upper_bound((uintptr_t)p);
+    if (it == e->pinned.begin()) return false;
+    --it;
+    return (uintptr_t)p >= it->first && (uintptr_t)p + bytes <= it->first + it->second;
+}
+
+// ------------------------------------------------------------------ device set-up
+template <typename Kern>
+int32_t set_smem_attr(Kern k, int bytes) {
+    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    return CTR_OK;
+}
+
+int32_t setup_kernel_attrs() {
+    int32_t rc;
+#define SET_GEMM(BN, EPI) \
+    if ((rc = set_smem_attr(gemm_f16_tcgen05_kernel<BN, EPI>, GemmCfg<BN>::kSmemBytes)) != CTR_OK) return rc;
+    SET_GEMM(256, EPI_RELU) SET_GEMM(128, EPI_RELU) SET_GEMM(256, EPI_CROSS) SET_GEMM(128, EPI_CROSS)
+    SET_GEMM(256, EPI_HEAD) SET_GEMM(128, EPI_HEAD)
+#undef SET_GEMM
+    return CTR_OK;
+}
+
+int32_t upload_gemm_layer(const float* W, const float* b, int N, int K, GemmLayer* L, cudaStream_t st) {
+    L->N = N;
+    L->Npad = round_up(N, 128);
+    L->Kpad = round_up(K, kBK);
+    L->BN = (L->Npad % 256 == 0) ? 256 : 128;
+    float* tmp = nullptr;
+    CUDA_TRY(cudaMalloc(&tmp, (size_t)N * K * sizeof(float)));
+    CUDA_TRY(cudaMemcpyAsync(tmp, W, (size_t)N * K * sizeof(float), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMalloc(&L->W, (size_t)L->Npad * L->Kpad * sizeof(__half)));
+    convert_pad_f16_kernel<<<1024, 256, 0, st>>>(tmp, N, K, L->W, L->Npad, L->Kpad);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMalloc(&L->bias, (size_t)L->Npad * sizeof(float)));
+    CUDA_TRY(cudaMemsetAsync(L->bias, 0, (size_t)L->Npad * sizeof(float), st));
+    CUDA_TRY(cudaMemcpyAsync(L->bias, b, (size_t)N * sizeof(float), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    CUDA_TRY(cudaFree(tmp));
+    return make_map_f16(&L->map_w, L->W, L->Npad, L->Kpad, L->Kpad, L->BN);
+}
+
+int32_t upload_padded_vec(const float* src, int n, int n_pad, float** dst, cudaStream_t st) {
+    CUDA_TRY(cudaMalloc(dst, (size_t)n_pad * sizeof(float)));
+    CUDA_TRY(cudaMemsetAsync(*dst, 0, (size_t)n_pad * sizeof(float), st));
+    if (n) CUDA_TRY(cudaMemcpyAsync(*dst, src, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return CTR_OK;
+}
+
+void free_model(DeviceModel& dm) {
+    cudaSetDevice(dm.dev);
+    cudaFree(dm.table);
+    for (auto* v : {&dm.mlp, &dm.cross})
+        for (auto& L : *v) { cudaFree(L.W); cudaFree(L.bias); }
+    cudaFree(dm.w_out_h);
+    cudaFree(dm.w_out_x);
+    dm = DeviceModel();
+}
+
+int32_t load_model_on_device(ctr_engine* e, int di, const HostWeights& hw) {
+    DeviceCtx& dc = *e->devs[di];
+    DeviceModel& dm = dc.model;
+    const ModelDesc& m = hw.m;
+    const int dev = e->cfg.device_ids[di];
+    CUDA_TRY(cudaSetDevice(dev));
+    dm.dev = dev;
+    CUDA_TRY(cudaDeviceGetAttribute(&dm.num_sms, cudaDevAttrMultiProcessorCount, dev));
+    cudaStream_t st = dc.main_stream;
+    const float* blob = hw.blob.data();
+    dm.b0 = blob[hw.off_b0];
+
+    const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1;
+    const uint64_t G = sharded ? (uint64_t)e->cfg.n_devices : 1;
+    const uint64_t local_rows = ((uint64_t)m.V + G - 1) / G;
+    const int shift = m.table_dtype == CTR_TABLE_FP32 ? 7 : 6;
+    dm.table_rows_local = local_rows;
+    dm.table_bytes = (size_t)local_rows << shift;
+    CUDA_TRY(cudaMalloc(&dm.table, dm.table_bytes));
+    if (m.table_mode == 1) {
+        const uint64_t ke = proc_key(m.seed, kTagE), kw = proc_key(m.seed, kTagW1);
+        const int grid = dm.num_sms * 8;
+        if (m.table_dtype == CTR_TABLE_FP32)
+            fill_table_procedural_kernel<0><<<grid, 256, 0, st>>>(dm.table, local_rows, G, (uint64_t)di % G, ke, kw, m.scale_e, m.scale_w1);
+        else
+            fill_table_procedural_kernel<1><<<grid, 256, 0, st>>>(dm.table, local_rows, G, (uint64_t)di % G, ke, kw, m.scale_e, m.scale_w1);
+        CUDA_TRY(cudaGetLastError());
+    } else {
+        // raw table: stream it through a bounded device staging buffer and pack on the device
+        const uint64_t chunk = 1u << 20;
+        float *t_emb = nullptr, *t_w1 = nullptr;
+        CUDA_TRY(cudaMalloc(&t_emb, chunk * kEmbDim * sizeof(float)));
+        CUDA_TRY(cudaMalloc(&t_w1, chunk * sizeof(float)));
+        std::vector<float> h_emb, h_w1;
+        for (uint64_t l0 = 0; l0 < local_rows; l0 += chunk) {
+            const uint64_t cnt = std::min<uint64_t>(chunk, local_rows - l0);
+            const float *src_e, *src_w;
+            uint64_t valid = cnt;
+            if (G == 1) {
+                src_e = blob + hw.off_emb + l0 * kEmbDim;
+                src_w = blob + hw.off_w1 + l0;
+            } else {                                   // local slot l holds global row l*G + di
+                h_emb.assign(cnt * kEmbDim, 0.f);
+                h_w1.assign(cnt, 0.f);
+                for (uint64_t l = 0; l < cnt; ++l) {
+                    const uint64_t row = (l0 + l) * G + (uint64_t)di;
+                    if (row >= (uint64_t)m.V) continue;
+                    memcpy(&h_emb[l * kEmbDim], blob + hw.off_emb + row * kEmbDim, kEmbDim * sizeof(float));
+                    h_w1[l] = blob[hw.off_w1 + row];
+                }
+                src_e = h_emb.data();
+                src_w = h_w1.data();
+            }
+            CUDA_TRY(cudaMemcpyAsync(t_emb, src_e, valid * kEmbDim * sizeof(float), cudaMemcpyHostToDevice, st));
+            CUDA_TRY(cudaMemcpyAsync(t_w1, src_w, valid * sizeof(float), cudaMemcpyHostToDevice, st));
+            if (m.table_dtype == CTR_TABLE_FP32) pack_table_kernel<0><<<1024, 256, 0, st>>>(dm.table, l0, t_emb, t_w1, cnt);
+            else pack_table_kernel<1><<<1024, 256, 0, st>>>(dm.table, l0, t_emb, t_w1, cnt);
+            CUDA_TRY(cudaGetLastError());
+            CUDA_TRY(cudaStreamSynchronize(st));
+        }
+        CUDA_TRY(cudaFree(t_emb));
+        CUDA_TRY(cudaFree(t_w1));
+    }
+    CUDA_TRY(cudaStreamSynchronize(st));
+
+    if (m.kind != CTR_MODEL_LR) {
+        int32_t rc;
+        int fan_in = m.d();
+        dm.mlp.resize(m.n_hidden);
+        for (int l = 0; l < m.n_hidden; ++l) {
+            // layer 0 reads X (K padded to d_pad); later layers read the previous padded width
+            if ((rc = upload_gemm_layer(blob + hw.off_mlp_w[l], blob + hw.off_mlp_b[l], m.hidden[l], fan_in, &dm.mlp[l], st)) != CTR_OK) return rc;
+            fan_in = m.hidden[l];
+        }
+        dm.cross.resize(m.n_cross);
+        for (int l = 0; l < m.n_cross; ++l)
+            if ((rc = upload_gemm_layer(blob + hw.off_cross_w[l], blob + hw.off_cross_b[l], m.d(), m.d(), &dm.cross[l], st)) != CTR_OK) return rc;
+        const float* w_out = blob + hw.off_wout;
+        const int h_last = m.hidden[m.n_hidden - 1];
+        const int x_part = m.kind == CTR_MODEL_DCN_V2 ? m.d() : 0;
+        if ((rc = upload_padded_vec(w_out + x_part, h_last, dm.mlp.back().Npad, &dm.w_out_h, st)) != CTR_OK) return rc;
+        if (x_part && (rc = upload_padded_vec(w_out, x_part, m.d_pad(), &dm.w_out_x, st)) != CTR_OK) return rc;
+        dm.b_out = blob[hw.off_bout];
+    }
+    dm.loaded = true;
+    return CTR_OK;
+}
+
+// ------------------------------------------------------------------ slots
+void free_slot(Slot& s) {
+    cudaSetDevice(s.dev);
+    cudaFree(s.d_ids); cudaFree(s.d_wts); cudaFree(s.d_scores); cudaFree(s.d_wide); cudaFree(s.d_extra); cudaFree(s.d_err);
+    for (auto*& b : s.buf) { cudaFree(b); b = nullptr; }
+    cudaFreeHost(s.h_ids); cudaFreeHost(s.h_wts); cudaFreeHost(s.h_scores); cudaFreeHost(s.h_err);
+    if (s.ev_ok) for (auto& ev : s.ev) cudaEventDestroy(ev);
+    if (s.join_ev) cudaEventDestroy(s.join_ev);
+    if (s.stream && s.owns_stream) cudaStreamDestroy(s.stream);
+    s = Slot();
+}
+
+// Allocates the model-dependent buffers of a slot and builds its GEMM plan.
+int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging) {
+    const ModelDesc& m = e->m;
+    DeviceModel& dm = dc.model;
+    CUDA_TRY(cudaSetDevice(dm.dev));
+    s.cap = e->cfg.max_candidates;
+    s.act_rows = round_up((int)std::min<int64_t>(s.cap, e->chunk_rows), kBM);
+    CUDA_TRY(cudaMalloc(&s.d_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
+    CUDA_TRY(cudaMalloc(&s.d_wts, (size_t)s.cap * m.F * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.d_scores, (size_t)s.cap * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.d_wide, (size_t)s.act_rows * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.d_extra, (size_t)s.act_rows * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.d_err, sizeof(int32_t)));
+    CUDA_TRY(cudaMemset(s.d_err, 0, sizeof(int32_t)));
+    if (host_staging) {
+        CUDA_TRY(cudaMallocHost(&s.h_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
+        CUDA_TRY(cudaMallocHost(&s.h_wts, (size_t)s.cap * m.F * sizeof(float)));
+        CUDA_TRY(cudaMallocHost(&s.h_scores, (size_t)s.cap * sizeof(float)));
+        CUDA_TRY(cudaMallocHost(&s.h_err, sizeof(int32_t)));
+    }
+    if (m.kind == CTR_MODEL_LR) return CTR_OK;
+
+    const int dpad = m.d_pad();
+    int maxn = 0;
+    for (auto& L : dm.mlp) maxn = std::max(maxn, L.Npad);
+    auto alloc_buf = [&](int id, int ldv) -> int32_t {
+        s.ld[id] = ldv;
+        CUDA_TRY(cudaMalloc(&s.buf[id], (size_t)s.act_rows * ldv * sizeof(__half)));
+        CUDA_TRY(cudaMemset(s.buf[id], 0, (size_t)s.act_rows * ldv * sizeof(__half)));   // pad columns stay zero
+        return CTR_OK;
+    };
+    int32_t rc;
+    if ((rc = alloc_buf(0, dpad)) != CTR_OK) return rc;
+    if ((rc = alloc_buf(1, maxn)) != CTR_OK) return rc;
+    if (dm.mlp.size() > 1 && (rc = alloc_buf(2, maxn)) != CTR_OK) return rc;
+    if (m.kind == CTR_MODEL_DCN_V2) {
+        if ((rc = alloc_buf(3, dpad)) != CTR_OK) return rc;
+        if (m.n_cross > 1 && (rc = alloc_buf(4, dpad)) != CTR_OK) return rc;
+    }
+
+    s.ops.clear();
+    auto add_op = [&](int kind, int layer, int epi, int a, int out, int xl) -> int32_t {
+        GemmOp op;
+        op.layer_kind = kind; op.layer = layer; op.epi = epi; op.a_buf = a; op.out_buf = out; op.xl_buf = xl;
+        const GemmLayer& L = kind == 0 ? dm.mlp[layer] : dm.cross[layer];
+        if (s.ld[a] < L.Kpad) return fail(CTR_ERR_INVALID, "internal: activation buffer narrower than the layer's K");
+        int32_t r = make_map_f16(&op.map_a, s.buf[a], (uint64_t)s.act_rows, (uint64_t)L.Kpad, (uint64_t)s.ld[a], kBM);
+        if (r != CTR_OK) return r;
+        s.ops.push_back(op);
+        return CTR_OK;
+    };
+    // cross network first (DCN-v2): x_{l+1} = x0 * (W x_l + b) + x_l
+    int xl = 0;
+    for (int l = 0; l < m.n_cross; ++l) {
+        const int out = 3 + (l & 1);
+        if ((rc = add_op(1, l, EPI_CROSS, xl, out, xl)) != CTR_OK) return rc;
+        xl = out;
+    }
+    // MLP on x0
+    int a = 0;
+    for (int l = 0; l < m.n_hidden; ++l) {
+        const GemmLayer& L = dm.mlp[l];
+        const bool last = l == m.n_hidden - 1;
+        const bool fuse_head = last && L.Npad == L.BN;      // whole layer width inside one tile
+        const int out = 1 + (l & 1);
+        if ((rc = add_op(0, l, fuse_head ? EPI_HEAD : EPI_RELU, a, out, -1)) != CTR_OK) return rc;
+        a = out;
+    }
+    return CTR_OK;
+}
+
+int32_t init_slot_common(Slot& s, int dev, cudaStream_t stream /*nullptr -> create*/) {
+    CUDA_TRY(cudaSetDevice(dev));
+    s.dev = dev;
+    if (stream) { s.stream = stream; s.owns_stream = false; }
+    else CUDA_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+    for (auto& ev : s.ev) CUDA_TRY(cudaEventCreate(&ev));
+    s.ev_ok = true;
+    CUDA_TRY(cudaEventCreateWithFlags(&s.join_ev, cudaEventDisableTiming));
+    return CTR_OK;
+}
+
+// ------------------------------------------------------------------ the device path for one chunk
+template <int TD, bool H, bool E, bool L, bool FM, bool S>
+void launch_gather_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    gather_pool_kernel<TD, H, E, L, FM, S><<<grid, kGatherThreads, smem, st>>>(gp);
+}
+
+template <int TD, bool H, bool S>
+void launch_gather_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    switch (kind) {
+        case CTR_MODEL_LR: launch_gather_t<TD, H, false, true, false, S>(gp, grid, smem, st); break;
+        case CTR_MODEL_WIDE_DEEP: launch_gather_t<TD, H, true, true, false, S>(gp, grid, smem, st); break;
+        case CTR_MODEL_DEEPFM: launch_gather_t<TD, H, true, true, true, S>(gp, grid, smem, st); break;
+        default: launch_gather_t<TD, H, true, false, false, S>(gp, grid, smem, st); break;
+    }
+}
+
+void launch_gather(const ModelDesc& m, bool sharded, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    const bool hashed = m.id_mode == CTR_ID_HASHED;
+    if (m.table_dtype == CTR_TABLE_FP32) {
+        if (sharded) { if (hashed) launch_gather_kind<0, true, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, false, true>(m.kind, gp, grid, smem, st); }
+        else { if (hashed) launch_gather_kind<0, true, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, false, false>(m.kind, gp, grid, smem, st); }
+    } else {
+        if (sharded) { if (hashed) launch_gather_kind<1, true, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, false, true>(m.kind, gp, grid, smem, st); }
+        else { if (hashed) launch_gather_kind<1, true, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, false, false>(m.kind, gp, grid, smem, st); }
+    }
+}
+
+template <int BN>
+void launch_gemm_bn(int epi, const CUtensorMap& ma, const CUtensorMap& mw, const GemmParams& gp, int grid, cudaStream_t st) {
+    const size_t smem = GemmCfg<BN>::kSmemBytes;
+    switch (epi) {
+        case EPI_RELU: gemm_f16_tcgen05_kernel<BN, EPI_RELU><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
+        case EPI_CROSS: gemm_f16_tcgen05_kernel<BN, EPI_CROSS><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
+        default: gemm_f16_tcgen05_kernel<BN, EPI_HEAD><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
+    }
+}
+
+void mark(ctr_engine* e, Slot& s, int stage) {
+    if (!e->timing || !s.time_this || s.n_ev >= 16) return;
+    s.ev_stage[s.n_ev] = stage;
+    cudaEventRecord(s.ev[s.n_ev++], s.stream);
+}
+
+// Scores rows [0, n) of (d_ids, d_wts) into d_scores on s.stream; n <= s.act_rows for tower models.
+int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int n, float* d_scores) {
+    const ModelDesc& m = e->m;
+    DeviceModel& dm = dc.model;
+    cudaStream_t st = s.stream;
+    const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1;
+
+    GatherParams gp;
+    memset(&gp, 0, sizeof(gp));
+    gp.ids = d_ids; gp.wts = d_wts; gp.n = n; gp.F = m.F;
+    gp.bulk_ok = ((reinterpret_cast<uintptr_t>(d_ids) | reinterpret_cast<uintptr_t>(d_wts)) & 15) == 0;
+    gp.table = dm.table; gp.num_rows = (uint64_t)m.V; gp.b0 = dm.b0;
+    gp.error_flag = s.d_err;
+    gp.n_shards = sharded ? e->cfg.n_devices : 1;
+    for (int g = 0; g < CTR_MAX_DEVICES; ++g) gp.shard_base[g] = e->shard_base[g];
+    if (m.kind == CTR_MODEL_LR) { gp.scores = d_scores; }
+    else { gp.X = s.buf[0]; gp.ldx = s.ld[0]; gp.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide; }
+    const int n_tiles = (n + kGatherTile - 1) / kGatherTile;
+    const int ggrid = std::max(1, std::min(n_tiles, dm.num_sms * 4));
+    const size_t gsmem = (size_t)2 * kGatherTile * m.F * 12;
+    mark(e, s, 0);
+    launch_gather(m, sharded, gp, ggrid, gsmem, st);
+    CUDA_TRY(cudaGetLastError());
+    e->launches.fetch_add(1, std::memory_order_relaxed);
+    if (m.kind == CTR_MODEL_LR) { mark(e, s, -2); return CTR_OK; }
+
+    const int xl_final = m.n_cross ? 3 + ((m.n_cross - 1) & 1) : -1;
+    bool head_fused = false;
+    int li = 0;
+    for (GemmOp& op : s.ops) {
+        const GemmLayer& L = op.layer_kind == 0 ? dm.mlp[op.layer] : dm.cross[op.layer];
+        GemmParams p;
+        memset(&p, 0, sizeof(p));
+        p.M = n; p.N = L.Npad; p.K = L.Kpad; p.bias = L.bias;
+        p.out = s.buf[op.out_buf]; p.ldo = s.ld[op.out_buf];
+        if (op.epi == EPI_CROSS) { p.x0 = s.buf[0]; p.xl = s.buf[op.xl_buf]; p.ldx = s.ld[0]; }
+        if (op.epi == EPI_HEAD) {
+            if (m.kind == CTR_MODEL_DCN_V2) {
+                // x_L part of the head first: extra[b] = w_x . x_L[b]
+                HeadParams hp;
+                memset(&hp, 0, sizeof(hp));
+                hp.n = n; hp.XL = s.buf[xl_final]; hp.ldxl = s.ld[xl_final]; hp.nx = m.d_pad(); hp.w_x = dm.w_out_x;
+                hp.extra_out = s.d_extra;
+                mark(e, s, 100);
+                head_kernel<<<std::min((n + 7) / 8, dm.num_sms * 8), 256, 0, st>>>(hp);
+                CUDA_TRY(cudaGetLastError());
+                e->launches.fetch_add(1, std::memory_order_relaxed);
+                p.extra = s.d_extra;
+            } else {
+                p.wide = s.d_wide;
+            }
+            p.w_out = dm.w_out_h; p.b_out = dm.b_out; p.scores = d_scores;
+            head_fused = true;
+        }
+        const int tiles = ((n + kBM - 1) / kBM) * (L.Npad / L.BN);
+        const int grid = std::max(1, std::min(tiles, dm.num_sms));
+        mark(e, s, ++li);
+        if (L.BN == 256) launch_gemm_bn<256>(op.epi, op.map_a, L.map_w, p, grid, st);
+        else launch_gemm_bn<128>(op.epi, op.map_a, L.map_w, p, grid, st);
+        CUDA_TRY(cudaGetLastError());
+        e->launches.fetch_add(1, std::memory_order_relaxed);
+    }
+    if (!head_fused) {
+        const GemmOp& last = s.ops.back();
+        HeadParams hp;
+        memset(&hp, 0, sizeof(hp));
+        hp.n = n; hp.H = s.buf[last.out_buf]; hp.ldh = s.ld[last.out_buf]; hp.nh = dm.mlp.back().Npad; hp.w_h = dm.w_out_h;
+        if (m.kind == CTR_MODEL_DCN_V2) { hp.XL = s.buf[xl_final]; hp.ldxl = s.ld[xl_final]; hp.nx = m.d_pad(); hp.w_x = dm.w_out_x; }
+        else hp.wide = s.d_wide;
+        hp.b_out = dm.b_out; hp.scores = d_scores;
+        mark(e, s, 100);
+        head_kernel<<<std::min((n + 7) / 8, dm.num_sms * 8), 256, 0, st>>>(hp);
+        CUDA_TRY(cudaGetLastError());
+        e->launches.fetch_add(1, std::memory_order_relaxed);
+    }
+    mark(e, s, -2);
+    return CTR_OK;
+}
+
+// Scores n candidates (device pointers) on slot s, chunked so activations stay in their buffers.
+int32_t score_on_slot(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int64_t n, float* d_scores) {
+    const int F = e->m.F;
+    const int64_t step = e->m.kind == CTR_MODEL_LR ? (int64_t)1 << 30 : s.act_rows;
+    s.n_ev = 0;
+    for (int64_t c0 = 0; c0 < n; c0 += step) {
+        const int cnt = (int)std::min<int64_t>(step, n - c0);
+        s.time_this = c0 == 0;                 // stage timing covers the first chunk only
+        int32_t rc = score_chunk(e, dc, s, d_ids + c0 * F, d_wts + c0 * F, cnt, d_scores + c0);
+        if (rc != CTR_OK) return rc;
+    }
+    return CTR_OK;
+}
+
+void collect_timing(Slot& s) {
+    s.n_stage = 0;
+    s.total_ms = -1.f;
+    if (s.n_ev < 2) { s.n_ev = 0; return; }
+    for (int i = 0; i + 1 < s.n_ev; ++i) {
+        if (s.ev_stage[i] == -2) continue;
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, s.ev[i], s.ev[i + 1]) == cudaSuccess && s.n_stage < 16) {
+            s.stage_ms[s.n_stage] = ms;
+            s.ev_stage[s.n_stage] = s.ev_stage[i];
+            ++s.n_stage;
+        }
+    }
+    float tot = 0.f;
+    if (cudaEventElapsedTime(&tot, s.ev[0], s.ev[s.n_ev - 1]) == cudaSuccess) s.total_ms = tot;
+    s.n_ev = 0;
+}
+
+// ------------------------------------------------------------------ request completion
+void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t status, const std::string& err) {
+    if (status != CTR_OK) {
+        int expected = CTR_OK;
+        if (r->status.compare_exchange_strong(expected, status)) {
+            std::lock_guard<std::mutex> lk(r->m);
+            r->error = err;
+        }
+    }
+    if (r->pending.fetch_sub(1) == 1) {
+        {
+            std::lock_guard<std::mutex> lk(r->m);
+            r->done = true;
+        }
+        r->cv.notify_all();
+        if (r->cb) r->cb(r->user, r->ticket, r->status.load());
+    }
+}
+
+// sendRequest (DC:91-115) for one shard: stage -> H2D -> kernels -> D2H -> hand back.
+void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
+    const ModelDesc& m = e->m;
+    auto body = [&]() -> int32_t {
+        CUDA_TRY(cudaSetDevice(s.dev));
+        const size_t ib = (size_t)t.n * m.F * sizeof(int64_t), wb = (size_t)t.n * m.F * sizeof(float), sb = (size_t)t.n * sizeof(float);
+        // The feature packer: caller buffers that came from ctr_alloc_pinned are DMA'd in place;
+        // pageable ones (a Java heap array, a numpy array) are packed into this slot's pinned slab.
+        const int64_t* src_ids = t.ids;
+        const float* src_wts = t.wts;
+        if (!is_pinned(e, t.ids, ib)) { memcpy(s.h_ids, t.ids, ib); src_ids = s.h_ids; }
+        if (!is_pinned(e, t.wts, wb)) { memcpy(s.h_wts, t.wts, wb); src_wts = s.h_wts; }
+        const bool out_pinned = is_pinned(e, t.scores, sb);
+        float* dst_scores = out_pinned ? t.scores : s.h_scores;
+        CUDA_TRY(cudaMemcpyAsync(s.d_ids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(s.d_wts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
+        int32_t rc = score_on_slot(e, dc, s, s.d_ids, s.d_wts, t.n, s.d_scores);
+        if (rc != CTR_OK) return rc;
+        CUDA_TRY(cudaMemcpyAsync(dst_scores, s.d_scores, sb, cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(s.h_err, s.d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        if (e->timing) collect_timing(s);
+        if (*s.h_err) {
+            CUDA_TRY(cudaMemsetAsync(s.d_err, 0, sizeof(int32_t), s.stream));
+            return fail(CTR_ERR_INVALID, "feature id out of range for a direct-indexed table");
+        }
+        if (!out_pinned) memcpy(t.scores, s.h_scores, sb);
+        return CTR_OK;
+    };
+    int32_t rc = body();
+    complete_shard(e, t.req, rc, rc == CTR_OK ? std::string() : g_last_error);
+}
+
+void worker_main(ctr_engine* e, DeviceCtx* dc, Slot* s) {
+    cudaSetDevice(s->dev);
+    for (;;) {
+        Task t;
+        {
+            std::unique_lock<std::mutex> lk(dc->q_mu);
+            dc->q_cv.wait(lk, [&] { return !dc->queue.empty(); });
+            t = dc->queue.front();
+            if (t.stop) return;                 // leave the stop marker for the other workers
+            dc->queue.pop_front();
+        }
+        run_task(e, *dc, *s, t);
+    }
+}
+
+void stop_workers(ctr_engine* e) {
+    for (auto& dcp : e->devs) {
+        DeviceCtx& dc = *dcp;
+        if (dc.threads.empty()) continue;
+        {
+            std::lock_guard<std::mutex> lk(dc.q_mu);
+            Task t; t.stop = true; t.ids = nullptr; t.wts = nullptr; t.n = 0; t.scores = nullptr;
+            dc.queue.push_back(t);
+        }
+        dc.q_cv.notify_all();
+        for (auto& th : dc.threads) th.join();
+        dc.threads.clear();
+        dc.queue.clear();
+    }
+}
+
+void free_device_state(ctr_engine* e) {
+    for (auto& dcp : e->devs) {
+        DeviceCtx& dc = *dcp;
+        for (auto& s : dc.worker_slots) free_slot(*s);
+        for (auto& s : dc.dev_slots) free_slot(*s);
+        dc.worker_slots.clear();
+        dc.dev_slots.clear();
+        if (dc.model.dev >= 0) free_model(dc.model);
+    }
+}
+
+}  // namespace
+
+// =========================================================================== C ABI
+extern "C" {
+
+const char* ctr_last_error(void) { return g_last_error.c_str(); }
+int32_t ctr_abi_version(void) { return CTR_ABI_VERSION; }
+
+int32_t ctr_partition_bounds(int64_t n, int32_t part_num, int64_t* begin, int64_t* end) {
+    if (part_num <= 0 || n < 0 || !begin || !end) return fail(CTR_ERR_INVALID, "ctr_partition_bounds: part_num must be positive");
+    split_bounds(n, part_num, begin, end);
+    return CTR_OK;
+}
+
+int32_t ctr_engine_create(const ctr_config* cfg, ctr_engine** out) {
+    if (!cfg || !out) return fail(CTR_ERR_INVALID, "ctr_engine_create: null argument");
+    if (cfg->struct_size != (int32_t)sizeof(ctr_config)) return fail(CTR_ERR_INVALID, "ctr_engine_create: ctr_config size mismatch (ABI)");
+    if (cfg->n_devices < 1 || cfg->n_devices > CTR_MAX_DEVICES) return fail(CTR_ERR_INVALID, "ctr_engine_create: n_devices must be 1..8");
+    if (cfg->max_candidates < 1) return fail(CTR_ERR_INVALID, "ctr_engine_create: max_candidates must be positive");
+    int count = 0;
+    cudaError_t ce = cudaGetDeviceCount(&count);
+    if (ce != cudaSuccess || count == 0) {
+        (void)cudaGetLastError();
+        return fail(CTR_ERR_CUDA, std::string("no usable CUDA device (there is no CPU fallback): ") + cudaGetErrorString(ce));
+    }
+    for (int i = 0; i < cfg->n_devices; ++i) {
+        if (cfg->device_ids[i] < 0 || cfg->device_ids[i] >= count) return fail(CTR_ERR_INVALID, "ctr_engine_create: device id out of range");
+        cudaDeviceProp prop;
+        CUDA_TRY(cudaGetDeviceProperties(&prop, cfg->device_ids[i]));
+        if (prop.major != 10) return fail(CTR_ERR_CUDA, std::string("device ") + prop.name + " is not sm_100: this engine has no other code path");
+    }
+    std::unique_ptr<ctr_engine> e(new ctr_engine());
+    e->cfg = *cfg;
+    if (e->cfg.workers_per_device <= 0) e->cfg.workers_per_device = 2;
+    if (const char* c = getenv("CTR_CHUNK_ROWS")) { int v = atoi(c); if (v >= 128) e->chunk_rows = round_up(v, 128); }
+    for (int i = 0; i < cfg->n_devices; ++i) {
+        std::unique_ptr<DeviceCtx> dc(new DeviceCtx());
+        CUDA_TRY(cudaSetDevice(cfg->device_ids[i]));
+        CUDA_TRY(cudaStreamCreateWithFlags(&dc->main_stream, cudaStreamNonBlocking));
+        CUDA_TRY(cudaEventCreateWithFlags(&dc->fork_ev, cudaEventDisableTiming));
+        int32_t rc = setup_kernel_attrs();
+        if (rc != CTR_OK) return rc;
+        dc->model.dev = -1;
+        e->devs.push_back(std::move(dc));
+    }
+    if (cfg->shard_mode == CTR_TABLES_ROW_SHARDED && cfg->n_devices > 1) {
+        for (int i = 0; i < cfg->n_devices; ++i)
+            for (int j = 0; j < cfg->n_devices; ++j) {
+                if (i == j) continue;
+                int can = 0;
+                CUDA_TRY(cudaDeviceCanAccessPeer(&can, cfg->device_ids[i], cfg->device_ids[j]));
+                if (!can) return fail(CTR_ERR_CUDA, "row-sharded tables need peer access between all devices");
+                CUDA_TRY(cudaSetDevice(cfg->device_ids[i]));
+                cudaError_t pe = cudaDeviceEnablePeerAccess(cfg->device_ids[j], 0);
+                if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) CUDA_TRY(pe);
+                (void)cudaGetLastError();
+            }
+    }
+    *out = e.release();
+    return CTR_OK;
+}
+
+int32_t ctr_engine_destroy(ctr_engine* e) {
+    if (!e) return CTR_OK;
+    e->shutting_down = true;
+    stop_workers(e);
+    free_device_state(e);
+    for (size_t i = 0; i < e->devs.size(); ++i) {
+        cudaSetDevice(e->cfg.device_ids[i]);
+        if (e->devs[i]->main_stream) cudaStreamDestroy(e->devs[i]->main_stream);
+        if (e->devs[i]->fork_ev) cudaEventDestroy(e->devs[i]->fork_ev);
+    }
+    {
+        std::lock_guard<std::mutex> lk(e->pin_mu);
+        for (auto& kv : e->pinned) cudaFreeHost(reinterpret_cast<void*>(kv.first));
+        e->pinned.clear();
+    }
+    delete e;
+    return CTR_OK;
+}
+
+int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
+    if (!e || !path) return fail(CTR_ERR_INVALID, "ctr_engine_load_weights: null argument");
+    HostWeights hw;
+    int32_t rc = read_weight_file(path, &hw);
+    if (rc != CTR_OK) return rc;
+    stop_workers(e);
+    free_device_state(e);
+    e->loaded = false;
+    e->m = hw.m;
+    for (int i = 0; i < e->cfg.n_devices; ++i) {
+        if ((rc = load_model_on_device(e, i, hw)) != CTR_OK) return rc;
+        e->shard_base[i] = e->devs[i]->model.table;
+    }
+    for (int i = 0; i < e->cfg.n_devices; ++i) {
+        DeviceCtx& dc = *e->devs[i];
+        const int dev = e->cfg.device_ids[i];
+        for (int w = 0; w < e->cfg.workers_per_device; ++w) {
+            std::unique_ptr<Slot> s(new Slot());
+            if ((rc = init_slot_common(*s, dev, nullptr)) != CTR_OK) return rc;
+            if ((rc = build_slot_plan(e, dc, *s, true)) != CTR_OK) return rc;
+            dc.worker_slots.push_back(std::move(s));
+        }
+        int n_dev_slots = 2;
+        if (const char* c = getenv("CTR_DEVICE_STREAMS")) { int v = atoi(c); if (v >= 1 && v <= 8) n_dev_slots = v; }
+        for (int w = 0; w < n_dev_slots; ++w) {
+            std::unique_ptr<Slot> s(new Slot());
+            if ((rc = init_slot_common(*s, dev, nullptr)) != CTR_OK) return rc;
+            if ((rc = build_slot_plan(e, dc, *s, false)) != CTR_OK) return rc;
+            dc.dev_slots.push_back(std::move(s));
+        }
+        CUDA_TRY(cudaDeviceSynchronize());
+    }
+    e->loaded = true;
+    for (int i = 0; i < e->cfg.n_devices; ++i) {
+        DeviceCtx& dc = *e->devs[i];
+        for (auto& s : dc.worker_slots) dc.threads.emplace_back(worker_main, e, &dc, s.get());
+    }
+    return CTR_OK;
+}
+
+int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out) {
+    if (!e || !out) return fail(CTR_ERR_INVALID, "ctr_engine_model_info: null argument");
+    if (!e->loaded) return fail(CTR_ERR_STATE, "weights not loaded");
+    memset(out, 0, sizeof(*out));
+    out->model_kind = e->m.kind; out->num_fields = e->m.F; out->emb_dim = e->m.K; out->id_mode = e->m.id_mode;
+    out->table_dtype = e->m.table_dtype; out->n_hidden = e->m.n_hidden;
+    for (int i = 0; i < CTR_MAX_HIDDEN; ++i) out->hidden[i] = e->m.hidden[i];
+    out->n_cross = e->m.n_cross; out->d_padded = e->m.d_pad(); out->num_rows = e->m.V;
+    out->table_bytes_per_device = (int64_t)e->devs[0]->model.table_bytes;
+    return CTR_OK;
+}
+
+int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out,
+                          ctr_callback cb, void* user, ctr_ticket* ticket) {
+    if (!e || !ticket) return fail(CTR_ERR_INVALID, "ctr_predict_async: null argument");
+    if (!e->loaded || e->shutting_down) return fail(CTR_ERR_STATE, "ctr_predict_async: weights not loaded or engine shutting down");
+    if (n_cand < 0 || (n_cand > 0 && (!ids || !wts || !scores_out))) return fail(CTR_ERR_INVALID, "ctr_predict_async: null buffer or negative count");
+    const int P = e->cfg.n_devices;
+    int64_t b[CTR_MAX_DEVICES], en[CTR_MAX_DEVICES];
+    split_bounds(n_cand, P, b, en);
+    for (int i = 0; i < P; ++i)
+        if (en[i] - b[i] > e->cfg.max_candidates)
+            return fail(CTR_ERR_CAPACITY, "ctr_predict_async: a shard exceeds max_candidates of this engine");
+    auto req = std::make_shared<Request>();
+    req->cb = cb; req->user = user;
+    req->ticket = e->next_ticket.fetch_add(1);
+    int shards = 0;
+    for (int i = 0; i < P; ++i) shards += en[i] > b[i];
+    {
+        std::lock_guard<std::mutex> lk(e->t_mu);
+        e->tickets[req->ticket] = req;
+    }
+    *ticket = req->ticket;
+    if (shards == 0) {                      // empty request: nothing to score, completes at once
+        req->pending = 1;
+        complete_shard(e, req, CTR_OK, "");
+        return CTR_OK;
+    }
+    req->pending = shards;
+    const int F = e->m.F;
+    for (int i = 0; i < P; ++i) {
+        if (en[i] == b[i]) continue;
+        Task t;
+        t.req = req; t.ids = ids + b[i] * F; t.wts = wts + b[i] * F; t.n = en[i] - b[i]; t.scores = scores_out + b[i];
+        DeviceCtx& dc = *e->devs[i];
+        {
+            std::lock_guard<std::mutex> lk(dc.q_mu);
+            dc.queue.push_back(t);
+        }
+        dc.q_cv.notify_one();
+    }
+    return CTR_OK;
+}
+
+int32_t ctr_wait(ctr_engine* e, ctr_ticket ticket, int32_t timeout_ms) {
+    if (!e) return fail(CTR_ERR_INVALID, "ctr_wait: null engine");
+    std::shared_ptr<Request> r;
+    {
+        std::lock_guard<std::mutex> lk(e->t_mu);
+        auto it = e->tickets.find(ticket);
+        if (it == e->tickets.end()) return fail(CTR_ERR_STATE, "ctr_wait: unknown or already released ticket");
+        r = it->second;
+    }
+    {
+        std::unique_lock<std::mutex> lk(r->m);
+        if (timeout_ms < 0) r->cv.wait(lk, [&] { return r->done; });
+        else if (!r->cv.wait_for(lk, std::chrono::milliseconds(timeout_ms), [&] { return r->done; }))
+            return fail(CTR_ERR_TIMEOUT, "ctr_wait: timed out");
+    }
+    {
+        std::lock_guard<std::mutex> lk(e->t_mu);
+        e->tickets.erase(ticket);
+    }
+    const int32_t st = r->status.load();
+    if (st != CTR_OK) return fail(st, r->error);
+    return CTR_OK;
+}
+
+int32_t ctr_predict(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out) {
+    ctr_ticket t;
+    int32_t rc = ctr_predict_async(e, ids, wts, n_cand, scores_out, nullptr, nullptr, &t);
+    if (rc != CTR_OK) return rc;
+    return ctr_wait(e, t, -1);
+}
+
+int32_t ctr_alloc_pinned(ctr_engine* e, int64_t bytes, void** out) {
+    if (!e || !out || bytes <= 0) return fail(CTR_ERR_INVALID, "ctr_alloc_pinned: bad argument");
+    void* p = nullptr;
+    CUDA_TRY(cudaSetDevice(e->cfg.device_ids[0]));
+    CUDA_TRY(cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocPortable));
+    std::lock_guard<std::mutex> lk(e->pin_mu);
+    e->pinned[(uintptr_t)p] = (size_t)bytes;
+    *out = p;
+    return CTR_OK;
+}
+
+int32_t ctr_free_pinned(ctr_engine* e, void* p) {
+    if (!e || !p) return fail(CTR_ERR_INVALID, "ctr_free_pinned: null argument");
+    {
+        std::lock_guard<std::mutex> lk(e->pin_mu);
+        auto it = e->pinned.find((uintptr_t)p);
+        if (it == e->pinned.end()) return fail(CTR_ERR_INVALID, "ctr_free_pinned: pointer was not allocated by ctr_alloc_pinned");
+        e->pinned.erase(it);
+    }
+    CUDA_TRY(cudaFreeHost(p));
+    return CTR_OK;
+}
+
+int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids, const void* d_wts, int64_t n_cand,
+                         void* d_scores, void* stream) {
+    if (!e) return fail(CTR_ERR_INVALID, "ctr_score_device: null engine");
+    if (!e->loaded) return fail(CTR_ERR_STATE, "ctr_score_device: weights not loaded");
+    if (device_index < 0 || device_index >= e->cfg.n_devices) return fail(CTR_ERR_INVALID, "ctr_score_device: device index out of range");
+    if (n_cand < 0 || (n_cand > 0 && (!d_ids || !d_wts || !d_scores))) return fail(CTR_ERR_INVALID, "ctr_score_device: null buffer or negative count");
+    if (n_cand == 0) return CTR_OK;
+    DeviceCtx& dc = *e->devs[device_index];
+    std::lock_guard<std::mutex> lk(dc.dev_mu);
+    CUDA_TRY(cudaSetDevice(dc.model.dev));
+    cudaStream_t user = reinterpret_cast<cudaStream_t>(stream);
+    cudaStream_t origin = user ? user : dc.main_stream;
+    const int F = e->m.F;
+    const int64_t* ids = static_cast<const int64_t*>(d_ids);
+    const float* wts = static_cast<const float*>(d_wts);
+    float* scores = static_cast<float*>(d_scores);
+    const int n_slots = (int)dc.dev_slots.size();
+    const int64_t step = e->m.kind == CTR_MODEL_LR ? n_cand : dc.dev_slots[0]->act_rows;
+    const int64_t n_chunks = (n_cand + step - 1) / step;
+    const int used = (int)std::min<int64_t>(n_slots, n_chunks);
+    // fork: the engine's streams start after whatever the caller queued on `origin`
+    CUDA_TRY(cudaEventRecord(dc.fork_ev, origin));
+    for (int w = 0; w < used; ++w) {
+        CUDA_TRY(cudaStreamWaitEvent(dc.dev_slots[w]->stream, dc.fork_ev, 0));
+        dc.dev_slots[w]->n_ev = 0;
+    }
+    for (int64_t c = 0; c < n_chunks; ++c) {
+        Slot& s = *dc.dev_slots[c % used];
+        const int64_t c0 = c * step;
+        const int cnt = (int)std::min<int64_t>(step, n_cand - c0);
+        s.time_this = c == 0;                              // stage timing: first chunk on slot 0 only
+        int32_t rc = score_chunk(e, dc, s, ids + c0 * F, wts + c0 * F, cnt, scores + c0);
+        if (rc != CTR_OK) return rc;
+    }
+    // join: `origin` continues after every engine stream has finished
+    for (int w = 0; w < used; ++w) {
+        CUDA_TRY(cudaEventRecord(dc.dev_slots[w]->join_ev, dc.dev_slots[w]->stream));
+        CUDA_TRY(cudaStreamWaitEvent(origin, dc.dev_slots[w]->join_ev, 0));
+    }
+    if (!user) {
+        CUDA_TRY(cudaStreamSynchronize(origin));
+        if (e->timing) collect_timing(*dc.dev_slots[0]);
+        int32_t err = 0;
+        for (int w = 0; w < used; ++w) {
+            int32_t v = 0;
+            CUDA_TRY(cudaMemcpy(&v, dc.dev_slots[w]->d_err, sizeof(v), cudaMemcpyDeviceToHost));
+            if (v) { err = 1; CUDA_TRY(cudaMemset(dc.dev_slots[w]->d_err, 0, sizeof(v))); }
+        }
+        if (err) return fail(CTR_ERR_INVALID, "feature id out of range for a direct-indexed table");
+    }
+    return CTR_OK;
+}
+
+int64_t ctr_engine_launch_count(ctr_engine* e) { return e ? e->launches.load() : 0; }
+
+int32_t ctr_engine_set_timing(ctr_engine* e, int32_t enabled) {
+    if (!e) return fail(CTR_ERR_INVALID, "null engine");
+    e->timing = enabled != 0;
+    return CTR_OK;
+}
+
+double ctr_engine_stage_ms(ctr_engine* e, int32_t device_index, int32_t stage) {
+    if (!e || device_index < 0 || device_index >= (int)e->devs.size() || e->devs[device_index]->dev_slots.empty()) return -1.0;
+    Slot& s = *e->devs[device_index]->dev_slots[0];
+    if (stage == -1) return s.total_ms;
+    for (int i = 0; i < s.n_stage; ++i)
+        if (s.ev_stage[i] == stage) return s.stage_ms[i];
+    return -1.0;
+}
+
+int32_t ctr_debug_read_rows(ctr_engine* e, int32_t device_index, const int64_t* rows, int64_t n, float* emb_out, float* w1_out) {
+    if (!e || !rows || !emb_out || !w1_out || n < 0) return fail(CTR_ERR_INVALID, "ctr_debug_read_rows: bad argument");
+    if (!e->loaded) return fail(CTR_ERR_STATE, "weights not loaded");
+    if (device_index < 0 || device_index >= e->cfg.n_devices) return fail(CTR_ERR_INVALID, "device index out of range");
+    if (n == 0) return CTR_OK;
+    DeviceModel& dm = e->devs[device_index]->model;
+    const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1;
+    const int64_t G = sharded ? e->cfg.n_devices : 1;
+    std::vector<int64_t> slots(n);
+    for (int64_t i = 0; i < n; ++i) {
+        if (rows[i] < 0 || rows[i] >= e->m.V) return fail(CTR_ERR_INVALID, "row out of range");
+        if (sharded && rows[i] % G != device_index) return fail(CTR_ERR_INVALID, "row is not held by this device's shard");
+        slots[i] = rows[i] / G;
+    }
+    CUDA_TRY(cudaSetDevice(dm.dev));
+    int64_t* d_slots; float *d_e, *d_w;
+    CUDA_TRY(cudaMalloc(&d_slots, n * sizeof(int64_t)));
+    CUDA_TRY(cudaMalloc(&d_e, n * kEmbDim * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&d_w, n * sizeof(float)));
+    CUDA_TRY(cudaMemcpy(d_slots, slots.data(), n * sizeof(int64_t), cudaMemcpyHostToDevice));
+    if (e->m.table_dtype == CTR_TABLE_FP32) read_rows_kernel<0><<<256, 256>>>(dm.table, d_slots, n, d_e, d_w);
+    else read_rows_kernel<1><<<256, 256>>>(dm.table, d_slots, n, d_e, d_w);
+    CUDA_TRY(cudaGetLastError());
+    CUDA_TRY(cudaMemcpy(emb_out, d_e, n * kEmbDim * sizeof(float), cudaMemcpyDeviceToHost));
+    CUDA_TRY(cudaMemcpy(w1_out, d_w, n * sizeof(float), cudaMemcpyDeviceToHost));
+    cudaFree(d_slots); cudaFree(d_e); cudaFree(d_w);
+    return CTR_OK;
+}
+
+int32_t ctr_debug_gemm(ctr_engine* e, int32_t device_index, const float* A, const float* W, const float* bias,
+                       int32_t M, int32_t N, int32_t K, int32_t relu, float* out) {
+    if (!e || !A || !W || !bias || !out || M < 1 || N < 1 || K < 1) return fail(CTR_ERR_INVALID, "ctr_debug_gemm: bad argument");
+    if (device_index < 0 || device_index >= e->cfg.n_devices) return fail(CTR_ERR_INVALID, "device index out of range");
+    (void)relu;
+    const int dev = e->cfg.device_ids[device_index];
+    CUDA_TRY(cudaSetDevice(dev));
+    int num_sms = 148;
+    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
+    cudaStream_t st = e->devs[device_index]->main_stream;
+    GemmLayer L;
+    int32_t rc = upload_gemm_layer(W, bias, N, K, &L, st);
+    if (rc != CTR_OK) return rc;
+    const int Mpad = round_up(M, kBM);
+    float* dA32 = nullptr; __half *dA = nullptr, *dO = nullptr;
+    CUDA_TRY(cudaMalloc(&dA32, (size_t)M * K * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&dA, (size_t)Mpad * L.Kpad * sizeof(__half)));
+    CUDA_TRY(cudaMalloc(&dO, (size_t)Mpad * L.Npad * sizeof(__half)));
+    CUDA_TRY(cudaMemcpyAsync(dA32, A, (size_t)M * K * sizeof(float), cudaMemcpyHostToDevice, st));
+    convert_pad_f16_kernel<<<1024, 256, 0, st>>>(dA32, M, K, dA, Mpad, L.Kpad);
+    CUDA_TRY(cudaGetLastError());
+    CUtensorMap map_a;
+    if ((rc = make_map_f16(&map_a, dA, (uint64_t)Mpad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, kBM)) != CTR_OK) return rc;
+    GemmParams p;
+    memset(&p, 0, sizeof(p));
+    p.M = M; p.N = L.Npad; p.K = L.Kpad; p.bias = L.bias; p.out = dO; p.ldo = L.Npad;
+    const int tiles = (Mpad / kBM) * (L.Npad / L.BN);
+    const int grid = std::max(1, std::min(tiles, num_sms));
+    if (L.BN == 256) launch_gemm_bn<256>(EPI_RELU, map_a, L.map_w, p, grid, st);
+    else launch_gemm_bn<128>(EPI_RELU, map_a, L.map_w, p, grid, st);
+    CUDA_TRY(cudaGetLastError());
+    e->launches.fetch_add(1, std::memory_order_relaxed);
+    std::vector<__half> h((size_t)M * L.Npad);
+    CUDA_TRY(cudaMemcpyAsync(h.data(), dO, h.size() * sizeof(__half), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    for (int m = 0; m < M; ++m)
+        for (int n = 0; n < N; ++n) out[(size_t)m * N + n] = __half2float(h[(size_t)m * L.Npad + n]);
+    cudaFree(dA32); cudaFree(dA); cudaFree(dO); cudaFree(L.W); cudaFree(L.bias);
+    return CTR_OK;
+}
+
+int32_t ctr_debug_gather(ctr_engine* e, int32_t device_index, const int64_t* ids, const float* wts, int64_t n,
+                         float* x_out, float* wide_out) {
+    if (!e || !ids || !wts || n < 1) return fail(CTR_ERR_INVALID, "ctr_debug_gather: bad argument");
+    if (!e->loaded) return fail(CTR_ERR_STATE, "weights not loaded");
+    if (device_index < 0 || device_index >= e->cfg.n_devices) return fail(CTR_ERR_INVALID, "device index out of range");
+    DeviceCtx& dc = *e->devs[device_index];
+    std::lock_guard<std::mutex> lk(dc.dev_mu);
+    Slot& s = *dc.dev_slots[0];
+    const ModelDesc& m = e->m;
+    if (n > s.act_rows || n > s.cap) return fail(CTR_ERR_CAPACITY, "ctr_debug_gather: n exceeds the chunk size");
+    CUDA_TRY(cudaSetDevice(s.dev));
+    CUDA_TRY(cudaMemcpyAsync(s.d_ids, ids, (size_t)n * m.F * sizeof(int64_t), cudaMemcpyHostToDevice, s.stream));
+    CUDA_TRY(cudaMemcpyAsync(s.d_wts, wts, (size_t)n * m.F * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+    // run the whole chunk (the gather is its first kernel), then read the gather's outputs back
+    s.time_this = false;
+    int32_t rc = score_chunk(e, dc, s, s.d_ids, s.d_wts, (int)n, s.d_scores);
+    if (rc != CTR_OK) return rc;
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    if (x_out && m.kind != CTR_MODEL_LR) {
+        std::vector<__half> h((size_t)n * s.ld[0]);
+        CUDA_TRY(cudaMemcpy(h.data(), s.buf[0], h.size() * sizeof(__half), cudaMemcpyDeviceToHost));
+        for (int64_t b = 0; b < n; ++b)
+            for (int j = 0; j < m.d(); ++j) x_out[b * m.d() + j] = __half2float(h[(size_t)b * s.ld[0] + j]);
+    }
+    if (wide_out && m.kind != CTR_MODEL_LR && m.kind != CTR_MODEL_DCN_V2)
+        CUDA_TRY(cudaMemcpy(wide_out, s.d_wide, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+    return CTR_OK;
+}
+
+}  // extern "C"

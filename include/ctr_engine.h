@@ -1,0 +1,162 @@
+/* ctr_engine.h -- C ABI of the B200-native CTR scoring engine.
+ *
+ * This is the drop-in boundary for ONE path of neuzxy/Distributed-TF-Serving: the client's
+ * "split candidates -> marshal -> score on N model replicas -> ordered merge" request
+ * (DCNClient.java:137-203).  Everything below replaces a piece of that path; each entry
+ * point cites the reference interface it stands in for.  DC = src/main/java/tensorflow/
+ * serving/DCNClient.java under the reference root.
+ *
+ * Conventions
+ *   - plain C types only (pointers, sizes, ints); no CUDA or torch types in any signature
+ *     (streams and device pointers cross as void*)
+ *   - every function returns CTR_OK (0) or a negative ctr_status; ctr_last_error() gives
+ *     the message of the last failure on the calling thread
+ *   - all entry points are thread-safe; the reference calls its path from 6 driver threads
+ *     fanning into a 16-thread pool (DC:31, DC:42, DC:213-224)
+ *   - layout is the reference's: ids int64 / wts float32, row-major [n_cand, F]
+ *     (DC:76-81, DC:97-108); scores float32 [n_cand] in input order (DC:161-164)
+ *   - there is no CPU fallback: without a usable CUDA device every call fails with
+ *     CTR_ERR_CUDA
+ */
+#ifndef CTR_ENGINE_H_
+#define CTR_ENGINE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CTR_ABI_VERSION 1
+#define CTR_MAX_DEVICES 8
+#define CTR_MAX_HIDDEN 4
+#define CTR_MAX_FIELDS 48
+
+typedef enum ctr_status {
+    CTR_OK = 0,
+    CTR_ERR_INVALID = -1,   /* bad argument / shape (the RPC's INVALID_ARGUMENT) */
+    CTR_ERR_CUDA = -2,      /* CUDA runtime / driver failure, message has the detail */
+    CTR_ERR_IO = -3,        /* weight file unreadable or malformed */
+    CTR_ERR_STATE = -4,     /* weights not loaded, engine shut down, unknown ticket */
+    CTR_ERR_TIMEOUT = -5,   /* ctr_wait ran out of time; the ticket stays valid */
+    CTR_ERR_CAPACITY = -6   /* request larger than the configured capacity */
+} ctr_status;
+
+/* Model family served behind sendRequest.  The reference addresses its model by the
+ * strings ("DCN", "serving_default") (DC:33-34, DC:83-88); here the family is an enum and
+ * there is no string lookup on the hot path. */
+typedef enum ctr_model_kind {
+    CTR_MODEL_LR = 0, CTR_MODEL_WIDE_DEEP = 1, CTR_MODEL_DEEPFM = 2, CTR_MODEL_DCN_V2 = 3
+} ctr_model_kind;
+
+typedef enum ctr_id_mode { CTR_ID_DIRECT = 0, CTR_ID_HASHED = 1 } ctr_id_mode;
+typedef enum ctr_table_dtype { CTR_TABLE_FP32 = 0, CTR_TABLE_F16 = 1 } ctr_table_dtype;
+typedef enum ctr_shard_mode {
+    CTR_TABLES_REPLICATED = 0,  /* candidates sharded over devices, tables on every device */
+    CTR_TABLES_ROW_SHARDED = 1  /* rows sharded (row mod n_devices); peers read over NVLink */
+} ctr_shard_mode;
+
+/* Replaces the reference's compile-time constants (DC:25-42): FIELD_NUM, candidateNum,
+ * hostsList (-> device_ids), the pool size. */
+typedef struct ctr_config {
+    int32_t struct_size;          /* sizeof(ctr_config), for ABI checking */
+    int32_t n_devices;            /* number of GPUs this engine fans out to (hostsList.size(), DC:38) */
+    int32_t device_ids[CTR_MAX_DEVICES];
+    int32_t max_candidates;       /* capacity of ONE request (candidateNum, DC:29) */
+    int32_t workers_per_device;   /* host threads (each with its own stream) per device; 0 = default 2 */
+    int32_t shard_mode;           /* ctr_shard_mode */
+    int32_t reserved[8];
+} ctr_config;
+
+typedef struct ctr_engine ctr_engine;
+typedef int64_t ctr_ticket;
+
+/* Completion callback (optional): runs on an engine thread when the request finishes,
+ * status is CTR_OK or the failure.  The Java shim completes its CompletableFuture here
+ * (normally or exceptionally), mirroring DC:151-159. */
+typedef void (*ctr_callback)(void* user, ctr_ticket ticket, int32_t status);
+
+/* ---- lifecycle: replaces getChannels()/shutDownChannels() (DC:118-135) ---- */
+int32_t ctr_engine_create(const ctr_config* cfg, ctr_engine** out);
+int32_t ctr_engine_destroy(ctr_engine* e);
+
+/* Loads a flat weight file (format: DESIGN.md "Weight file") on every device of the
+ * engine.  Stands in for TF-Serving loading the SavedModel named at DC:33-34.  The model
+ * family, field count, layer sizes and table description come from the file header. */
+int32_t ctr_engine_load_weights(ctr_engine* e, const char* path);
+
+/* Model description after load (F is what the reference calls FIELD_NUM, DC:25). */
+typedef struct ctr_model_info {
+    int32_t model_kind, num_fields, emb_dim, id_mode, table_dtype, n_hidden;
+    int32_t hidden[CTR_MAX_HIDDEN];
+    int32_t n_cross, d_padded;
+    int64_t num_rows;
+    int64_t table_bytes_per_device;
+} ctr_model_info;
+int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out);
+
+/* ---- the request: replaces processARequest (DC:137-203) minus the sort ----
+ * Splits n_cand candidates over the engine's devices by the reference rule
+ * (range = n_cand / n_devices, remainder to the last shard; DC:46-55 applied to
+ * candidates), scores every shard on its device (sendRequest, DC:91-115) and writes
+ * scores_out[j] for candidate j (ordered merge, DC:161-164).  Does not block on the GPU:
+ * returns a ticket at once.  ids / wts / scores_out stay owned by the caller and must
+ * stay valid until the ticket completes; ids/wts may be shared read-only between
+ * concurrent requests (as the reference shares its subList views, DC:219).  Buffers from
+ * ctr_alloc_pinned are used in place (no staging copy). */
+int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand,
+                          float* scores_out, ctr_callback cb, void* user, ctr_ticket* ticket);
+
+/* Blocks like CompletableFuture.join (DC:158-159).  timeout_ms < 0 waits for ever.  On
+ * CTR_OK or a failure status the ticket is released; on CTR_ERR_TIMEOUT it stays valid. */
+int32_t ctr_wait(ctr_engine* e, ctr_ticket ticket, int32_t timeout_ms);
+
+/* Synchronous convenience: ctr_predict_async + ctr_wait. */
+int32_t ctr_predict(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out);
+
+/* ---- pinned host memory for the zero-copy packer (north star (a)) ---- */
+int32_t ctr_alloc_pinned(ctr_engine* e, int64_t bytes, void** out);
+int32_t ctr_free_pinned(ctr_engine* e, void* p);
+
+/* ---- device-resident scoring: sendRequest (DC:91-115) with tensors already in HBM ----
+ * d_ids / d_wts / d_scores are device pointers on device_ids[device_index]; stream is a
+ * cudaStream_t (NULL = the engine's own stream for that device, and the call then returns
+ * after the work has finished).  Used by bench.py's device-resident figure and by callers
+ * that produce features on the GPU. */
+int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids, const void* d_wts,
+                         int64_t n_cand, void* d_scores, void* stream);
+
+/* ---- split rule, exported so a host can mirror the reference's partitionList ----
+ * DC:46-55: begin/end for part i of n elements in part_num parts. */
+int32_t ctr_partition_bounds(int64_t n, int32_t part_num, int64_t* begin, int64_t* end);
+
+/* ---- introspection ---- */
+const char* ctr_last_error(void);
+int32_t ctr_abi_version(void);
+/* Kernels launched by this engine since creation (all devices). */
+int64_t ctr_engine_launch_count(ctr_engine* e);
+/* Device time of the named stage of the most recent ctr_score_device call on that device,
+ * in milliseconds (CUDA events on the launching stream).  stage: 0 = gather/pool,
+ * 1..n = tower GEMM layer n, 100 = head, -1 = whole call.  Requires timing to be enabled
+ * with ctr_engine_set_timing(e, 1); returns a negative value otherwise. */
+int32_t ctr_engine_set_timing(ctr_engine* e, int32_t enabled);
+double ctr_engine_stage_ms(ctr_engine* e, int32_t device_index, int32_t stage);
+/* Test hook: copies table rows (embedding as float32 [n,K], first-order weight [n]) back
+ * from device memory of device_index, after the table dtype has been applied. */
+int32_t ctr_debug_read_rows(ctr_engine* e, int32_t device_index, const int64_t* rows, int64_t n,
+                            float* emb_out, float* w1_out);
+
+/* Test hook: one tower layer in isolation through the tcgen05 GEMM kernel.
+ * out[m, n] = max(sum_k half(A[m,k]) * half(W[n,k]) + bias[n], 0) rounded to half; host pointers,
+ * A [M,K], W [N,K] (the [out, in] layout of the weight file), out [M,N]. */
+int32_t ctr_debug_gemm(ctr_engine* e, int32_t device_index, const float* A, const float* W, const float* bias,
+                       int32_t M, int32_t N, int32_t K, int32_t relu, float* out);
+/* Test hook: the gather/pool kernel's outputs for n candidates (host pointers): x_out float32
+ * [n, F*16] (the half activations widened), wide_out [n] (lin, + FM for DeepFM); either may be NULL. */
+int32_t ctr_debug_gather(ctr_engine* e, int32_t device_index, const int64_t* ids, const float* wts, int64_t n,
+                         float* x_out, float* wide_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CTR_ENGINE_H_ */
