@@ -35,7 +35,7 @@ class CtrModelInfo(C.Structure):
     _fields_ = [("model_kind", C.c_int32), ("num_fields", C.c_int32), ("emb_dim", C.c_int32), ("id_mode", C.c_int32),
                 ("table_dtype", C.c_int32), ("n_hidden", C.c_int32), ("hidden", C.c_int32 * CTR_MAX_HIDDEN),
                 ("n_cross", C.c_int32), ("d_padded", C.c_int32), ("num_rows", C.c_int64),
-                ("table_bytes_per_device", C.c_int64)]
+                ("table_bytes_per_device", C.c_int64), ("chunk_rows", C.c_int32), ("reserved", C.c_int32)]
 
 
 CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int32)

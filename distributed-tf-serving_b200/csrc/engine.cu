@@ -207,10 +207,12 @@ struct Slot {
     std::vector<GemmOp> ops;
     // pinned staging for pageable callers
     int64_t* h_ids = nullptr; float* h_wts = nullptr; float* h_scores = nullptr; int32_t* h_err = nullptr;
-    // timing
-    cudaEvent_t ev[16]; bool ev_ok = false; int n_ev = 0; int ev_stage[16]; bool time_this = false;
+    // stage timing: a ring of event sets, one set per timed call (first chunk of the call only)
+    static constexpr int kTimeSets = 32, kTimeMarks = 12;
+    cudaEvent_t (*tev)[kTimeMarks] = nullptr;      // [kTimeSets][kTimeMarks], created when timing is switched on
+    int mark_stage[kTimeMarks]; int n_marks = 0;   // stage id of mark i (same sequence every call)
+    int cur_mark = 0; int sets_recorded = 0; bool time_this = false;
     cudaEvent_t join_ev = nullptr;
-    float stage_ms[16]; int n_stage = 0; float total_ms = -1.f;
 };
 
 struct Request {
@@ -251,7 +253,7 @@ struct ctr_engine {
     ModelDesc m;
     bool loaded = false;
     bool timing = false;
-    int chunk_rows = 16384;
+    int chunk_rows = 0;          // 0 = num_sms * 128
     std::vector<std::unique_ptr<DeviceCtx>> devs;
     std::mutex t_mu;
     std::unordered_map<ctr_ticket, std::shared_ptr<Request>> tickets;
@@ -430,7 +432,10 @@ void free_slot(Slot& s) {
     cudaFree(s.d_ids); cudaFree(s.d_wts); cudaFree(s.d_scores); cudaFree(s.d_wide); cudaFree(s.d_extra); cudaFree(s.d_err);
     for (auto*& b : s.buf) { cudaFree(b); b = nullptr; }
     cudaFreeHost(s.h_ids); cudaFreeHost(s.h_wts); cudaFreeHost(s.h_scores); cudaFreeHost(s.h_err);
-    if (s.ev_ok) for (auto& ev : s.ev) cudaEventDestroy(ev);
+    if (s.tev) {
+        for (int i = 0; i < Slot::kTimeSets; ++i) for (int j = 0; j < Slot::kTimeMarks; ++j) cudaEventDestroy(s.tev[i][j]);
+        delete[] s.tev;
+    }
     if (s.join_ev) cudaEventDestroy(s.join_ev);
     if (s.stream && s.owns_stream) cudaStreamDestroy(s.stream);
     s = Slot();
@@ -442,7 +447,9 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     DeviceModel& dm = dc.model;
     CUDA_TRY(cudaSetDevice(dm.dev));
     s.cap = e->cfg.max_candidates;
-    s.act_rows = round_up((int)std::min<int64_t>(s.cap, e->chunk_rows), kBM);
+    // default chunk: one 128-row tile per SM, so every tower layer runs in whole waves
+    const int chunk = e->chunk_rows > 0 ? e->chunk_rows : dm.num_sms * kBM;
+    s.act_rows = round_up((int)std::min<int64_t>(s.cap, chunk), kBM);
     CUDA_TRY(cudaMalloc(&s.d_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
     CUDA_TRY(cudaMalloc(&s.d_wts, (size_t)s.cap * m.F * sizeof(float)));
     CUDA_TRY(cudaMalloc(&s.d_scores, (size_t)s.cap * sizeof(float)));
@@ -512,8 +519,6 @@ int32_t init_slot_common(Slot& s, int dev, cudaStream_t stream /*nullptr -> crea
     s.dev = dev;
     if (stream) { s.stream = stream; s.owns_stream = false; }
     else CUDA_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-    for (auto& ev : s.ev) CUDA_TRY(cudaEventCreate(&ev));
-    s.ev_ok = true;
     CUDA_TRY(cudaEventCreateWithFlags(&s.join_ev, cudaEventDisableTiming));
     return CTR_OK;
 }
@@ -555,10 +560,12 @@ void launch_gemm_bn(int epi, const CUtensorMap& ma, const CUtensorMap& mw, const
     }
 }
 
+// Records a CUDA event on the launching stream in front of a stage (stage -2 = end of chunk).
 void mark(ctr_engine* e, Slot& s, int stage) {
-    if (!e->timing || !s.time_this || s.n_ev >= 16) return;
-    s.ev_stage[s.n_ev] = stage;
-    cudaEventRecord(s.ev[s.n_ev++], s.stream);
+    if (!e->timing || !s.time_this || !s.tev || s.sets_recorded >= Slot::kTimeSets || s.cur_mark >= Slot::kTimeMarks) return;
+    s.mark_stage[s.cur_mark] = stage;
+    cudaEventRecord(s.tev[s.sets_recorded][s.cur_mark++], s.stream);
+    if (stage == -2) { s.n_marks = s.cur_mark; s.cur_mark = 0; ++s.sets_recorded; s.time_this = false; }
 }
 
 // Scores rows [0, n) of (d_ids, d_wts) into d_scores on s.stream; n <= s.act_rows for tower models.
@@ -644,32 +651,30 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
 int32_t score_on_slot(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int64_t n, float* d_scores) {
     const int F = e->m.F;
     const int64_t step = e->m.kind == CTR_MODEL_LR ? (int64_t)1 << 30 : s.act_rows;
-    s.n_ev = 0;
     for (int64_t c0 = 0; c0 < n; c0 += step) {
         const int cnt = (int)std::min<int64_t>(step, n - c0);
-        s.time_this = c0 == 0;                 // stage timing covers the first chunk only
+        s.time_this = false;                   // stage timing is for ctr_score_device calls
         int32_t rc = score_chunk(e, dc, s, d_ids + c0 * F, d_wts + c0 * F, cnt, d_scores + c0);
         if (rc != CTR_OK) return rc;
     }
     return CTR_OK;
 }
 
-void collect_timing(Slot& s) {
-    s.n_stage = 0;
-    s.total_ms = -1.f;
-    if (s.n_ev < 2) { s.n_ev = 0; return; }
-    for (int i = 0; i + 1 < s.n_ev; ++i) {
-        if (s.ev_stage[i] == -2) continue;
-        float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, s.ev[i], s.ev[i + 1]) == cudaSuccess && s.n_stage < 16) {
-            s.stage_ms[s.n_stage] = ms;
-            s.ev_stage[s.n_stage] = s.ev_stage[i];
-            ++s.n_stage;
+// Mean device time of `stage` over the recorded sets (caller has synchronised the device).
+double mean_stage_ms(Slot& s, int stage) {
+    if (!s.tev || s.sets_recorded == 0 || s.n_marks < 2) return -1.0;
+    double sum = 0.0; int cnt = 0;
+    for (int set = 0; set < s.sets_recorded; ++set) {
+        double acc = 0.0; bool any = false;
+        for (int i = 0; i + 1 < s.n_marks; ++i) {
+            if (stage != -1 && s.mark_stage[i] != stage) continue;
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, s.tev[set][i], s.tev[set][i + 1]) != cudaSuccess) { (void)cudaGetLastError(); any = false; break; }
+            acc += ms; any = true;
         }
+        if (any) { sum += acc; ++cnt; }
     }
-    float tot = 0.f;
-    if (cudaEventElapsedTime(&tot, s.ev[0], s.ev[s.n_ev - 1]) == cudaSuccess) s.total_ms = tot;
-    s.n_ev = 0;
+    return cnt ? sum / cnt : -1.0;
 }
 
 // ------------------------------------------------------------------ request completion
@@ -712,7 +717,6 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
         CUDA_TRY(cudaMemcpyAsync(dst_scores, s.d_scores, sb, cudaMemcpyDeviceToHost, s.stream));
         CUDA_TRY(cudaMemcpyAsync(s.h_err, s.d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         CUDA_TRY(cudaStreamSynchronize(s.stream));
-        if (e->timing) collect_timing(s);
         if (*s.h_err) {
             CUDA_TRY(cudaMemsetAsync(s.d_err, 0, sizeof(int32_t), s.stream));
             return fail(CTR_ERR_INVALID, "feature id out of range for a direct-indexed table");
@@ -896,6 +900,7 @@ int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out) {
     for (int i = 0; i < CTR_MAX_HIDDEN; ++i) out->hidden[i] = e->m.hidden[i];
     out->n_cross = e->m.n_cross; out->d_padded = e->m.d_pad(); out->num_rows = e->m.V;
     out->table_bytes_per_device = (int64_t)e->devs[0]->model.table_bytes;
+    out->chunk_rows = e->devs[0]->dev_slots.empty() ? 0 : e->devs[0]->dev_slots[0]->act_rows;
     return CTR_OK;
 }
 
@@ -1017,15 +1022,12 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
     const int used = (int)std::min<int64_t>(n_slots, n_chunks);
     // fork: the engine's streams start after whatever the caller queued on `origin`
     CUDA_TRY(cudaEventRecord(dc.fork_ev, origin));
-    for (int w = 0; w < used; ++w) {
-        CUDA_TRY(cudaStreamWaitEvent(dc.dev_slots[w]->stream, dc.fork_ev, 0));
-        dc.dev_slots[w]->n_ev = 0;
-    }
+    for (int w = 0; w < used; ++w) CUDA_TRY(cudaStreamWaitEvent(dc.dev_slots[w]->stream, dc.fork_ev, 0));
     for (int64_t c = 0; c < n_chunks; ++c) {
         Slot& s = *dc.dev_slots[c % used];
         const int64_t c0 = c * step;
         const int cnt = (int)std::min<int64_t>(step, n_cand - c0);
-        s.time_this = c == 0;                              // stage timing: first chunk on slot 0 only
+        if (c == 0) { s.time_this = true; s.cur_mark = 0; }  // stage timing: first chunk (slot 0) only
         int32_t rc = score_chunk(e, dc, s, ids + c0 * F, wts + c0 * F, cnt, scores + c0);
         if (rc != CTR_OK) return rc;
     }
@@ -1036,7 +1038,6 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
     }
     if (!user) {
         CUDA_TRY(cudaStreamSynchronize(origin));
-        if (e->timing) collect_timing(*dc.dev_slots[0]);
         int32_t err = 0;
         for (int w = 0; w < used; ++w) {
             int32_t v = 0;
@@ -1052,17 +1053,27 @@ int64_t ctr_engine_launch_count(ctr_engine* e) { return e ? e->launches.load() :
 
 int32_t ctr_engine_set_timing(ctr_engine* e, int32_t enabled) {
     if (!e) return fail(CTR_ERR_INVALID, "null engine");
+    if (!e->loaded) return fail(CTR_ERR_STATE, "weights not loaded");
+    for (auto& dcp : e->devs) {
+        std::lock_guard<std::mutex> lk(dcp->dev_mu);
+        Slot& s = *dcp->dev_slots[0];
+        CUDA_TRY(cudaSetDevice(s.dev));
+        if (enabled && !s.tev) {
+            s.tev = new cudaEvent_t[Slot::kTimeSets][Slot::kTimeMarks];
+            for (int i = 0; i < Slot::kTimeSets; ++i) for (int j = 0; j < Slot::kTimeMarks; ++j) CUDA_TRY(cudaEventCreate(&s.tev[i][j]));
+        }
+        s.sets_recorded = 0; s.cur_mark = 0; s.n_marks = 0; s.time_this = false;    // (re)start the averaging window
+    }
     e->timing = enabled != 0;
     return CTR_OK;
 }
 
 double ctr_engine_stage_ms(ctr_engine* e, int32_t device_index, int32_t stage) {
     if (!e || device_index < 0 || device_index >= (int)e->devs.size() || e->devs[device_index]->dev_slots.empty()) return -1.0;
-    Slot& s = *e->devs[device_index]->dev_slots[0];
-    if (stage == -1) return s.total_ms;
-    for (int i = 0; i < s.n_stage; ++i)
-        if (s.ev_stage[i] == stage) return s.stage_ms[i];
-    return -1.0;
+    DeviceCtx& dc = *e->devs[device_index];
+    std::lock_guard<std::mutex> lk(dc.dev_mu);
+    cudaSetDevice(dc.model.dev);
+    return mean_stage_ms(*dc.dev_slots[0], stage);
 }
 
 int32_t ctr_debug_read_rows(ctr_engine* e, int32_t device_index, const int64_t* rows, int64_t n, float* emb_out, float* w1_out) {

@@ -92,6 +92,8 @@ typedef struct ctr_model_info {
     int32_t n_cross, d_padded;
     int64_t num_rows;
     int64_t table_bytes_per_device;
+    int32_t chunk_rows;           /* candidates the tower kernels process per launch */
+    int32_t reserved;
 } ctr_model_info;
 int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out);
 
@@ -135,10 +137,12 @@ const char* ctr_last_error(void);
 int32_t ctr_abi_version(void);
 /* Kernels launched by this engine since creation (all devices). */
 int64_t ctr_engine_launch_count(ctr_engine* e);
-/* Device time of the named stage of the most recent ctr_score_device call on that device,
- * in milliseconds (CUDA events on the launching stream).  stage: 0 = gather/pool,
- * 1..n = tower GEMM layer n, 100 = head, -1 = whole call.  Requires timing to be enabled
- * with ctr_engine_set_timing(e, 1); returns a negative value otherwise. */
+/* Stage timing.  ctr_engine_set_timing(e, 1) starts (or restarts) an averaging window: each
+ * following ctr_score_device call records CUDA events on the launching stream around every
+ * kernel of its FIRST chunk (up to 32 calls per window).  After the caller has synchronised,
+ * ctr_engine_stage_ms gives the mean device time in milliseconds of one stage over the window:
+ * stage 0 = gather/pool, 1..n = n-th tower GEMM of the plan, 100 = head kernel, -1 = the whole
+ * first chunk.  Negative when nothing was recorded. */
 int32_t ctr_engine_set_timing(ctr_engine* e, int32_t enabled);
 double ctr_engine_stage_ms(ctr_engine* e, int32_t device_index, int32_t stage);
 /* Test hook: copies table rows (embedding as float32 [n,K], first-order weight [n]) back
