@@ -16,13 +16,14 @@ ERR_NAMES = {-1: "CTR_ERR_INVALID", -2: "CTR_ERR_CUDA", -3: "CTR_ERR_IO", -4: "C
              -5: "CTR_ERR_TIMEOUT", -6: "CTR_ERR_CAPACITY"}
 CTR_MAX_DEVICES, CTR_MAX_HIDDEN = 8, 4
 TABLES_REPLICATED, TABLES_ROW_SHARDED = 0, 1
+STATIC_MAX_CANDIDATES = 1024
 
 # every symbol include/ctr_engine.h declares (tests check the library exports exactly these)
 EXPORTS = ["ctr_engine_create", "ctr_engine_destroy", "ctr_engine_load_weights", "ctr_engine_model_info",
            "ctr_predict_async", "ctr_wait", "ctr_predict", "ctr_alloc_pinned", "ctr_free_pinned",
            "ctr_score_device", "ctr_partition_bounds", "ctr_last_error", "ctr_abi_version",
            "ctr_engine_launch_count", "ctr_engine_set_timing", "ctr_engine_stage_ms", "ctr_debug_read_rows",
-           "ctr_debug_gemm", "ctr_debug_gather"]
+           "ctr_debug_gemm", "ctr_debug_gather", "ctr_score_device_static"]
 
 
 class CtrConfig(C.Structure):
@@ -70,6 +71,7 @@ def load_library() -> C.CDLL:
     lib.ctr_alloc_pinned.argtypes = [vp, i64, C.POINTER(vp)]
     lib.ctr_free_pinned.argtypes = [vp, vp]
     lib.ctr_score_device.argtypes = [vp, i32, vp, vp, i64, vp, vp]
+    lib.ctr_score_device_static.argtypes = [vp, i32, vp, vp, i64, vp, vp]
     lib.ctr_partition_bounds.argtypes = [i64, i32, vp, vp]
     lib.ctr_last_error.restype = C.c_char_p
     lib.ctr_engine_launch_count.argtypes = [vp]
@@ -199,6 +201,11 @@ class Engine:
     def score_device(self, d_ids: int, d_wts: int, n_cand: int, d_scores: int, stream: int = 0, device_index: int = 0):
         """Raw device pointers (ints) and a cudaStream_t handle (0 = engine stream, blocking)."""
         _check(self.lib.ctr_score_device(self.handle, device_index, d_ids, d_wts, n_cand, d_scores, stream or None))
+
+    def score_device_static(self, d_ids: int, d_wts: int, n_cand: int, d_scores: int, stream: int = 0, device_index: int = 0):
+        """ctr_score_device_static: same as score_device, but the engine allocates nothing; the
+        activations live in the library's fixed scratch (<= STATIC_MAX_CANDIDATES per call)."""
+        _check(self.lib.ctr_score_device_static(self.handle, device_index, d_ids, d_wts, n_cand, d_scores, stream or None))
 
     def launch_count(self) -> int:
         return int(self.lib.ctr_engine_launch_count(self.handle))

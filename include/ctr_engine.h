@@ -128,6 +128,24 @@ int32_t ctr_free_pinned(ctr_engine* e, void* p);
 int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids, const void* d_wts,
                          int64_t n_cand, void* d_scores, void* stream);
 
+/* ---- device-resident scoring without any allocation (no counterpart in the reference) ----
+ * Same contract and same results as ctr_score_device, for callers that must not allocate GPU
+ * memory or enter the driver's allocator on the request path: processes whose HBM is already
+ * owned in full by another pool, and latency-critical threads for which a cudaMalloc (which can
+ * stall every stream of the device) is not acceptable.  The intermediate activations live in
+ * one fixed __device__ array inside the library image (about 8.5 MB, resident on every GPU that
+ * loads the library until the process exits), so a call handles at most
+ * CTR_STATIC_MAX_CANDIDATES candidates (models with d_padded <= 768, hidden widths <= 1024);
+ * larger requests fail with CTR_ERR_CAPACITY.  The call itself performs no cudaMalloc / cudaFree.
+ * The first call on a GPU looks up the array's device address (once per GPU); make that first
+ * call before starting any stream capture.  All calls on a GPU share the array, which keeps the
+ * previous call's contents (what has to start at zero is cleared on `stream` at the start of each
+ * call): calls whose GPU work overlaps in time race -- order them on one stream or with events.
+ * stream == NULL runs on the engine's stream and returns when the scores are ready. */
+#define CTR_STATIC_MAX_CANDIDATES 1024
+int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, const void* d_ids, const void* d_wts,
+                                int64_t n_cand, void* d_scores, void* stream);
+
 /* ---- split rule, exported so a host can mirror the reference's partitionList ----
  * DC:46-55: begin/end for part i of n elements in part_num parts. */
 int32_t ctr_partition_bounds(int64_t n, int32_t part_num, int64_t* begin, int64_t* end);
