@@ -100,3 +100,58 @@ def predict(engine: "binding.Engine", ids: np.ndarray, wts: np.ndarray) -> np.nd
     """The whole of processARequest (minus the sort) as ONE engine call: the engine splits
     the candidates over its GPUs by the DC:46-55 rule and merges in order."""
     return engine.predict(np.ascontiguousarray(ids, np.int64), np.ascontiguousarray(wts, np.float32))
+
+
+# ---------------------------------------------------------------------------- one process per GPU
+def shard_for_rank(n_cand: int, world: int, rank: int):
+    """Candidate range of ``rank`` under the DC:46-55 rule (remainder to the last rank)."""
+    return binding.partition_bounds(n_cand, world)[rank]
+
+
+def processARequestDistributed(score_fn, ids, wts, field_num: int, group=None, src: int = 0):
+    """processARequest (DC:137-203, minus the sort) when every GPU has its own process
+    (``torchrun``; NCCL on the GPU box, gloo in CPU tests): rank ``src`` holds the request, every
+    rank scores its DC:46-55 shard with ``score_fn(ids[n,F], wts[n,F]) -> float32[n]`` (on a GPU
+    box: ``engine.predict``), and the shards come back to ``src`` in rank order, so output index j
+    is candidate j (DC:161-164).  Returns the merged scores on ``src`` and ``None`` elsewhere.
+    The only collectives are the scatter of inputs and the gather of scores; the scoring itself
+    needs no exchange."""
+    import torch
+    import torch.distributed as dist
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    meta = [int(np.asarray(ids).size // field_num) if rank == src else 0]
+    dist.broadcast_object_list(meta, src=src, group=group)
+    n = meta[0]
+    bounds = binding.partition_bounds(n, world)
+    a, b = bounds[rank]
+    my_ids = torch.empty(((b - a) * field_num,), dtype=torch.int64)
+    my_wts = torch.empty(((b - a) * field_num,), dtype=torch.float32)
+    if rank == src:
+        fi = torch.from_numpy(np.ascontiguousarray(ids, np.int64).reshape(-1))
+        fw = torch.from_numpy(np.ascontiguousarray(wts, np.float32).reshape(-1))
+        parts_i = [fi[s * field_num:e * field_num].contiguous() for s, e in bounds]
+        parts_w = [fw[s * field_num:e * field_num].contiguous() for s, e in bounds]
+    # shards are ragged (the last one takes the remainder): point-to-point instead of scatter
+    if rank == src:
+        reqs = []
+        for r in range(world):
+            if r == src:
+                my_ids.copy_(parts_i[r]); my_wts.copy_(parts_w[r])
+            else:
+                reqs += [dist.isend(parts_i[r], r, group=group), dist.isend(parts_w[r], r, group=group)]
+        [q.wait() for q in reqs]
+    else:
+        dist.recv(my_ids, src, group=group)
+        dist.recv(my_wts, src, group=group)
+    local = torch.from_numpy(np.ascontiguousarray(
+        score_fn(my_ids.numpy().reshape(-1, field_num), my_wts.numpy().reshape(-1, field_num)), np.float32))
+    if rank == src:
+        out = torch.empty(n, dtype=torch.float32)
+        for r, (s, e) in enumerate(bounds):
+            if r == src:
+                out[s:e] = local
+            else:
+                dist.recv(out[s:e], r, group=group)
+        return out.numpy()
+    dist.send(local, src, group=group)
+    return None
