@@ -169,7 +169,7 @@ struct GemmLayer {
     int N = 0, Npad = 0, Kpad = 0, BN = 0;
     __half* W = nullptr;      // [Npad, Kpad]
     float* bias = nullptr;    // [Npad]
-    CUtensorMap map_w;
+    CUtensorMap map_w_pair;   // box {64, BN/2}: each CTA of a pair loads half of the W tile
 };
 
 struct DeviceModel {
@@ -293,11 +293,11 @@ int32_t set_smem_attr(Kern k, int bytes) {
 
 int32_t setup_kernel_attrs() {
     int32_t rc;
-#define SET_GEMM(BN, EPI) \
-    if ((rc = set_smem_attr(gemm_f16_tcgen05_kernel<BN, EPI>, GemmCfg<BN>::kSmemBytes)) != CTR_OK) return rc;
-    SET_GEMM(256, EPI_RELU) SET_GEMM(128, EPI_RELU) SET_GEMM(256, EPI_CROSS) SET_GEMM(128, EPI_CROSS)
-    SET_GEMM(256, EPI_HEAD) SET_GEMM(128, EPI_HEAD)
-#undef SET_GEMM
+#define SET_PAIR(BN, EPI) \
+    if ((rc = set_smem_attr(gemm_f16_pair_kernel<BN, EPI>, GemmPairCfg<BN>::kSmemBytes)) != CTR_OK) return rc;
+    SET_PAIR(256, EPI_RELU) SET_PAIR(128, EPI_RELU) SET_PAIR(256, EPI_CROSS) SET_PAIR(128, EPI_CROSS)
+    SET_PAIR(256, EPI_HEAD) SET_PAIR(128, EPI_HEAD)
+#undef SET_PAIR
     return CTR_OK;
 }
 
@@ -317,7 +317,7 @@ int32_t upload_gemm_layer(const float* W, const float* b, int N, int K, GemmLaye
     CUDA_TRY(cudaMemcpyAsync(L->bias, b, (size_t)N * sizeof(float), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     CUDA_TRY(cudaFree(tmp));
-    return make_map_f16(&L->map_w, L->W, L->Npad, L->Kpad, L->Kpad, L->BN);
+    return make_map_f16(&L->map_w_pair, L->W, L->Npad, L->Kpad, L->Kpad, L->BN / 2);
 }
 
 int32_t upload_padded_vec(const float* src, int n, int n_pad, float** dst, cudaStream_t st) {
@@ -551,16 +551,23 @@ void launch_gather(const ModelDesc& m, bool sharded, const GatherParams& gp, int
 }
 
 template <int BN>
-void launch_gemm_bn(int epi, const CUtensorMap& ma, const CUtensorMap& mw, const GemmParams& gp, int grid, cudaStream_t st) {
-    const size_t smem = GemmCfg<BN>::kSmemBytes;
+void launch_gemm_pair_bn(int epi, const CUtensorMap& ma, const CUtensorMap& mw, const GemmParams& gp, int grid, cudaStream_t st) {
+    const size_t smem = GemmPairCfg<BN>::kSmemBytes;
     switch (epi) {
-        case EPI_RELU: gemm_f16_tcgen05_kernel<BN, EPI_RELU><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
-        case EPI_CROSS: gemm_f16_tcgen05_kernel<BN, EPI_CROSS><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
-        default: gemm_f16_tcgen05_kernel<BN, EPI_HEAD><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
+        case EPI_RELU: gemm_f16_pair_kernel<BN, EPI_RELU><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
+        case EPI_CROSS: gemm_f16_pair_kernel<BN, EPI_CROSS><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
+        default: gemm_f16_pair_kernel<BN, EPI_HEAD><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
     }
 }
 
-// Records a CUDA event on the launching stream in front of a stage (stage -2 = end of chunk).
+// One tower layer on `st`: CTA pairs over 256-row tiles, one pair per TPC, persistent.
+void launch_gemm(const GemmLayer& L, int epi, const CUtensorMap& map_a, const GemmParams& p, int rows, int num_sms, cudaStream_t st) {
+    const int tiles = ((rows + 2 * kBM - 1) / (2 * kBM)) * (L.Npad / L.BN);
+    const int grid = 2 * std::max(1, std::min(tiles, num_sms / 2));
+    if (L.BN == 256) launch_gemm_pair_bn<256>(epi, map_a, L.map_w_pair, p, grid, st);
+    else launch_gemm_pair_bn<128>(epi, map_a, L.map_w_pair, p, grid, st);
+}
+
 void mark(ctr_engine* e, Slot& s, int stage) {
     if (!e->timing || !s.time_this || !s.tev || s.sets_recorded >= Slot::kTimeSets || s.cur_mark >= Slot::kTimeMarks) return;
     s.mark_stage[s.cur_mark] = stage;
@@ -622,11 +629,8 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
             p.w_out = dm.w_out_h; p.b_out = dm.b_out; p.scores = d_scores;
             head_fused = true;
         }
-        const int tiles = ((n + kBM - 1) / kBM) * (L.Npad / L.BN);
-        const int grid = std::max(1, std::min(tiles, dm.num_sms));
         mark(e, s, ++li);
-        if (L.BN == 256) launch_gemm_bn<256>(op.epi, op.map_a, L.map_w, p, grid, st);
-        else launch_gemm_bn<128>(op.epi, op.map_a, L.map_w, p, grid, st);
+        launch_gemm(L, op.epi, op.map_a, p, n, dm.num_sms, st);
         CUDA_TRY(cudaGetLastError());
         e->launches.fetch_add(1, std::memory_order_relaxed);
     }
@@ -1118,7 +1122,7 @@ int32_t ctr_debug_gemm(ctr_engine* e, int32_t device_index, const float* A, cons
     GemmLayer L;
     int32_t rc = upload_gemm_layer(W, bias, N, K, &L, st);
     if (rc != CTR_OK) return rc;
-    const int Mpad = round_up(M, kBM);
+    const int Mpad = round_up(M, 2 * kBM);
     float* dA32 = nullptr; __half *dA = nullptr, *dO = nullptr;
     CUDA_TRY(cudaMalloc(&dA32, (size_t)M * K * sizeof(float)));
     CUDA_TRY(cudaMalloc(&dA, (size_t)Mpad * L.Kpad * sizeof(__half)));
@@ -1131,11 +1135,29 @@ int32_t ctr_debug_gemm(ctr_engine* e, int32_t device_index, const float* A, cons
     GemmParams p;
     memset(&p, 0, sizeof(p));
     p.M = M; p.N = L.Npad; p.K = L.Kpad; p.bias = L.bias; p.out = dO; p.ldo = L.Npad;
-    const int tiles = (Mpad / kBM) * (L.Npad / L.BN);
-    const int grid = std::max(1, std::min(tiles, num_sms));
-    if (L.BN == 256) launch_gemm_bn<256>(EPI_RELU, map_a, L.map_w, p, grid, st);
-    else launch_gemm_bn<128>(EPI_RELU, map_a, L.map_w, p, grid, st);
+    long long* d_prof = nullptr;
+    const bool prof = getenv("CTR_GEMM_PROF") != nullptr;
+    if (prof) {
+        CUDA_TRY(cudaMalloc(&d_prof, (size_t)num_sms * 8 * sizeof(long long)));
+        CUDA_TRY(cudaMemsetAsync(d_prof, 0, (size_t)num_sms * 8 * sizeof(long long), st));
+        p.prof = d_prof;
+        launch_gemm(L, EPI_RELU, map_a, p, M, num_sms, st);        // warm-up (cold L2 / descriptors)
+    }
+    launch_gemm(L, EPI_RELU, map_a, p, M, num_sms, st);
     CUDA_TRY(cudaGetLastError());
+    if (prof) {
+        std::vector<long long> h((size_t)num_sms * 8);
+        CUDA_TRY(cudaMemcpyAsync(h.data(), d_prof, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        const char* names[7] = {"producer wait empty", "mma wait acc_empty", "mma wait full", "mma issue+commit", "mma loop total", "epi wait acc_full", "epi body"};
+        fprintf(stderr, "[gemm prof] M=%d N=%d K=%d BN=%d (cycles; CTA0 leader / CTA1 peer / CTA2 / mean over leaders)\n", M, N, K, L.BN);
+        for (int i = 0; i < 7; ++i) {
+            double mean = 0; int cnt = 0;
+            for (int c = 0; c < num_sms; c += 2) if (h[c * 8 + 4]) { mean += (double)h[c * 8 + i]; ++cnt; }
+            fprintf(stderr, "  %-22s %10lld %10lld %10lld   mean %.0f\n", names[i], h[i], h[8 + i], h[16 + i], cnt ? mean / cnt : 0.0);
+        }
+        cudaFree(d_prof);
+    }
     e->launches.fetch_add(1, std::memory_order_relaxed);
     std::vector<__half> h((size_t)M * L.Npad);
     CUDA_TRY(cudaMemcpyAsync(h.data(), dO, h.size() * sizeof(__half), cudaMemcpyDeviceToHost, st));
