@@ -8,11 +8,11 @@
 //   threadPool       DC:42       -> worker threads, one CUDA stream each, per device
 //   getChannels      DC:118-125  -> ctr_engine_create (one "channel" per GPU)
 // The model arithmetic the reference delegates to an external SavedModel is the CUDA path in
-// gather.cuh / gemm_f16.cuh.  There is no CPU fallback anywhere.
+// gather.cuh / tower.cuh.  There is no CPU fallback anywhere.
 #include "../../include/ctr_engine.h"
 #include "common.cuh"
 #include "gather.cuh"
-#include "gemm_f16.cuh"
+#include "tower.cuh"
 
 #include <atomic>
 #include <chrono>
@@ -135,7 +135,8 @@ int32_t read_weight_file(const char* path, HostWeights* hw) {
     for (int i = 0; i < m.n_hidden; ++i)
         if (m.hidden[i] < 8 || m.hidden[i] % 8) return bad("hidden sizes must be positive multiples of 8");
     if (m.kind != CTR_MODEL_DCN_V2) m.n_cross = 0;
-    if (m.n_cross < 0 || m.n_cross > 8) return bad("cross layer count out of range");
+    if (m.n_cross < 0 || m.n_cross > 4) return bad("cross layer count out of range (0..4)");
+    if (m.kind == CTR_MODEL_DCN_V2 && m.n_cross < 1) return bad("DCN-v2 needs at least one cross layer");
 
     size_t n = 1;
     hw->off_b0 = 0;
@@ -166,10 +167,9 @@ int32_t read_weight_file(const char* path, HostWeights* hw) {
 
 // ------------------------------------------------------------------ per-device model state
 struct GemmLayer {
-    int N = 0, Npad = 0, Kpad = 0, BN = 0;
+    int N = 0, Npad = 0, Kpad = 0;
     __half* W = nullptr;      // [Npad, Kpad]
     float* bias = nullptr;    // [Npad]
-    CUtensorMap map_w_pair;   // box {64, BN/2}: each CTA of a pair loads half of the W tile
 };
 
 struct DeviceModel {
@@ -185,12 +185,12 @@ struct DeviceModel {
     bool loaded = false;
 };
 
-struct GemmOp {
-    int layer_kind;   // 0 mlp, 1 cross
-    int layer;
-    int epi;
-    int a_buf, out_buf, xl_buf;    // buffer ids: 0 X, 1 H0, 2 H1, 3 XL0, 4 XL1
-    CUtensorMap map_a;
+// One launch of tower_chain_kernel: a sequence of layers, each feeding the next.
+struct Chain {
+    int BN = 256;
+    int n_layers = 0;
+    ChainMaps maps;
+    ChainParams params;       // template: M / score pointer are filled per launch
 };
 
 // One stream with its private activation buffers ("slot"): everything a shard needs on the device.
@@ -199,12 +199,13 @@ struct Slot {
     cudaStream_t stream = nullptr;
     bool owns_stream = true;
     int64_t cap = 0;           // candidate capacity of the id/weight/score buffers
-    int act_rows = 0;          // rows of the activation buffers (chunk size)
+    int x_rows = 0;            // candidates per launch: rows of X / wide / extra (multiple of 256)
+    int scratch_rows = 0;      // rows of the per-pair scratch (resident CTA pairs x 256)
     int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;
     float* d_wide = nullptr; float* d_extra = nullptr; int32_t* d_err = nullptr;
     __half* buf[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     int ld[5] = {0, 0, 0, 0, 0};
-    std::vector<GemmOp> ops;
+    std::vector<Chain> chains;
     // pinned staging for pageable callers
     int64_t* h_ids = nullptr; float* h_wts = nullptr; float* h_scores = nullptr; int32_t* h_err = nullptr;
     // stage timing: a ring of event sets, one set per timed call (first chunk of the call only)
@@ -293,11 +294,8 @@ int32_t set_smem_attr(Kern k, int bytes) {
 
 int32_t setup_kernel_attrs() {
     int32_t rc;
-#define SET_PAIR(BN, EPI) \
-    if ((rc = set_smem_attr(gemm_f16_pair_kernel<BN, EPI>, GemmPairCfg<BN>::kSmemBytes)) != CTR_OK) return rc;
-    SET_PAIR(256, EPI_RELU) SET_PAIR(128, EPI_RELU) SET_PAIR(256, EPI_CROSS) SET_PAIR(128, EPI_CROSS)
-    SET_PAIR(256, EPI_HEAD) SET_PAIR(128, EPI_HEAD)
-#undef SET_PAIR
+    if ((rc = set_smem_attr(tower_chain_kernel<256>, ChainCfg<256>::kSmemBytes)) != CTR_OK) return rc;
+    if ((rc = set_smem_attr(tower_chain_kernel<128>, ChainCfg<128>::kSmemBytes)) != CTR_OK) return rc;
     return CTR_OK;
 }
 
@@ -305,7 +303,6 @@ int32_t upload_gemm_layer(const float* W, const float* b, int N, int K, GemmLaye
     L->N = N;
     L->Npad = round_up(N, 128);
     L->Kpad = round_up(K, kBK);
-    L->BN = (L->Npad % 256 == 0) ? 256 : 128;
     float* tmp = nullptr;
     CUDA_TRY(cudaMalloc(&tmp, (size_t)N * K * sizeof(float)));
     CUDA_TRY(cudaMemcpyAsync(tmp, W, (size_t)N * K * sizeof(float), cudaMemcpyHostToDevice, st));
@@ -317,7 +314,7 @@ int32_t upload_gemm_layer(const float* W, const float* b, int N, int K, GemmLaye
     CUDA_TRY(cudaMemcpyAsync(L->bias, b, (size_t)N * sizeof(float), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     CUDA_TRY(cudaFree(tmp));
-    return make_map_f16(&L->map_w_pair, L->W, L->Npad, L->Kpad, L->Kpad, L->BN / 2);
+    return CTR_OK;
 }
 
 int32_t upload_padded_vec(const float* src, int n, int n_pad, float** dst, cudaStream_t st) {
@@ -441,20 +438,76 @@ void free_slot(Slot& s) {
     s = Slot();
 }
 
-// Allocates the model-dependent buffers of a slot and builds its GEMM plan.
+// Builds the chains of a slot from buffers that already exist (no allocation in here: the
+// static-scratch entry point calls this too).
+//   buf[0] X [x_rows, d_pad]   buf[1], buf[2] MLP scratch [scratch_rows, maxn]   buf[3], buf[4] cross scratch [scratch_rows, d_pad]
+int32_t build_chains(ctr_engine* e, DeviceModel& dm, Slot& s) {
+    const ModelDesc& m = e->m;
+    s.chains.clear();
+    if (m.kind == CTR_MODEL_LR) return CTR_OK;
+    int32_t rc;
+    auto make_chain = [&](const std::vector<GemmLayer>& layers, bool is_cross) -> int32_t {
+        Chain c;
+        memset(&c.params, 0, sizeof(c.params));
+        c.n_layers = (int)layers.size();
+        if (c.n_layers > kMaxChain) return fail(CTR_ERR_INVALID, "a chain holds at most 4 layers");
+        c.BN = 256;
+        for (auto& L : layers) if (L.Npad % 256) c.BN = 128;
+        int a = 0;                                            // buffer id of the current layer's A operand
+        for (int l = 0; l < c.n_layers; ++l) {
+            const GemmLayer& L = layers[l];
+            const bool last = l == c.n_layers - 1;
+            const int out = is_cross ? 3 + (l & 1) : 1 + (l & 1);
+            if (s.ld[a] < L.Kpad) return fail(CTR_ERR_INVALID, "internal: activation buffer narrower than the layer's K");
+            const int a_rows = a == 0 ? s.x_rows : s.scratch_rows;
+            if ((rc = make_map_f16(&c.maps.a[l], s.buf[a], (uint64_t)a_rows, (uint64_t)L.Kpad, (uint64_t)s.ld[a], kBM)) != CTR_OK) return rc;
+            if ((rc = make_map_f16(&c.maps.w[l], L.W, (uint64_t)L.Npad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, c.BN / 2)) != CTR_OK) return rc;
+            ChainLayer& cl = c.params.layer[l];
+            cl.N = L.Npad; cl.K = L.Kpad; cl.a_global = a == 0; cl.bias = L.bias; cl.a_ptr = s.buf[a]; cl.lda = s.ld[a];
+            cl.out_global = 0;
+            if (last) {
+                cl.epi = is_cross ? EPI_CROSS_DOT : EPI_HEAD;
+                cl.w_out = is_cross ? dm.w_out_x : dm.w_out_h;
+                cl.out = nullptr; cl.ldo = 0;
+            } else {
+                cl.epi = is_cross ? EPI_CROSS : EPI_RELU;
+                cl.out = s.buf[out]; cl.ldo = s.ld[out];
+            }
+            a = out;
+        }
+        c.params.n_layers = c.n_layers;
+        c.params.x0 = s.buf[0]; c.params.ldx0 = s.ld[0];
+        c.params.b_out = dm.b_out;
+        if (is_cross) {
+            c.params.extra_out = s.d_extra;                   // w_x . x_L, consumed by the MLP chain's head
+        } else {
+            c.params.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide;
+            c.params.extra_in = m.kind == CTR_MODEL_DCN_V2 ? s.d_extra : nullptr;
+        }
+        s.chains.push_back(c);
+        return CTR_OK;
+    };
+    if (m.kind == CTR_MODEL_DCN_V2 && (rc = make_chain(dm.cross, true)) != CTR_OK) return rc;
+    return make_chain(dm.mlp, false);
+}
+
+// Allocates the model-dependent buffers of a slot and builds its plan.
 int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging) {
     const ModelDesc& m = e->m;
     DeviceModel& dm = dc.model;
     CUDA_TRY(cudaSetDevice(dm.dev));
     s.cap = e->cfg.max_candidates;
-    // default chunk: one 128-row tile per SM, so every tower layer runs in whole waves
-    const int chunk = e->chunk_rows > 0 ? e->chunk_rows : dm.num_sms * kBM;
-    s.act_rows = round_up((int)std::min<int64_t>(s.cap, chunk), kBM);
+    const int pairs = dm.num_sms / 2;
+    // rows per launch: host-request slots hold one request; device-resident slots default to 8 tiles per
+    // CTA pair (8 x 74 x 256 = 151 552 candidates, X = 194 MB), CTR_CHUNK_ROWS overrides
+    const int want = host_staging ? (int)s.cap : (e->chunk_rows > 0 ? e->chunk_rows : 8 * pairs * 2 * kBM);
+    s.x_rows = round_up(std::max(want, 1), 2 * kBM);
+    s.scratch_rows = std::min(pairs, s.x_rows / (2 * kBM)) * 2 * kBM;
     CUDA_TRY(cudaMalloc(&s.d_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
     CUDA_TRY(cudaMalloc(&s.d_wts, (size_t)s.cap * m.F * sizeof(float)));
     CUDA_TRY(cudaMalloc(&s.d_scores, (size_t)s.cap * sizeof(float)));
-    CUDA_TRY(cudaMalloc(&s.d_wide, (size_t)s.act_rows * sizeof(float)));
-    CUDA_TRY(cudaMalloc(&s.d_extra, (size_t)s.act_rows * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.d_wide, (size_t)s.x_rows * sizeof(float)));
+    CUDA_TRY(cudaMalloc(&s.d_extra, (size_t)s.x_rows * sizeof(float)));
     CUDA_TRY(cudaMalloc(&s.d_err, sizeof(int32_t)));
     CUDA_TRY(cudaMemset(s.d_err, 0, sizeof(int32_t)));
     if (host_staging) {
@@ -468,50 +521,21 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     const int dpad = m.d_pad();
     int maxn = 0;
     for (auto& L : dm.mlp) maxn = std::max(maxn, L.Npad);
-    auto alloc_buf = [&](int id, int ldv) -> int32_t {
+    auto alloc_buf = [&](int id, int rows, int ldv) -> int32_t {
         s.ld[id] = ldv;
-        CUDA_TRY(cudaMalloc(&s.buf[id], (size_t)s.act_rows * ldv * sizeof(__half)));
-        CUDA_TRY(cudaMemset(s.buf[id], 0, (size_t)s.act_rows * ldv * sizeof(__half)));   // pad columns stay zero
+        CUDA_TRY(cudaMalloc(&s.buf[id], (size_t)rows * ldv * sizeof(__half)));
+        CUDA_TRY(cudaMemset(s.buf[id], 0, (size_t)rows * ldv * sizeof(__half)));   // pad columns stay zero
         return CTR_OK;
     };
     int32_t rc;
-    if ((rc = alloc_buf(0, dpad)) != CTR_OK) return rc;
-    if ((rc = alloc_buf(1, maxn)) != CTR_OK) return rc;
-    if (dm.mlp.size() > 1 && (rc = alloc_buf(2, maxn)) != CTR_OK) return rc;
+    if ((rc = alloc_buf(0, s.x_rows, dpad)) != CTR_OK) return rc;
+    if ((rc = alloc_buf(1, s.scratch_rows, maxn)) != CTR_OK) return rc;
+    if ((rc = alloc_buf(2, s.scratch_rows, maxn)) != CTR_OK) return rc;
     if (m.kind == CTR_MODEL_DCN_V2) {
-        if ((rc = alloc_buf(3, dpad)) != CTR_OK) return rc;
-        if (m.n_cross > 1 && (rc = alloc_buf(4, dpad)) != CTR_OK) return rc;
+        if ((rc = alloc_buf(3, s.scratch_rows, dpad)) != CTR_OK) return rc;
+        if ((rc = alloc_buf(4, s.scratch_rows, dpad)) != CTR_OK) return rc;
     }
-
-    s.ops.clear();
-    auto add_op = [&](int kind, int layer, int epi, int a, int out, int xl) -> int32_t {
-        GemmOp op;
-        op.layer_kind = kind; op.layer = layer; op.epi = epi; op.a_buf = a; op.out_buf = out; op.xl_buf = xl;
-        const GemmLayer& L = kind == 0 ? dm.mlp[layer] : dm.cross[layer];
-        if (s.ld[a] < L.Kpad) return fail(CTR_ERR_INVALID, "internal: activation buffer narrower than the layer's K");
-        int32_t r = make_map_f16(&op.map_a, s.buf[a], (uint64_t)s.act_rows, (uint64_t)L.Kpad, (uint64_t)s.ld[a], kBM);
-        if (r != CTR_OK) return r;
-        s.ops.push_back(op);
-        return CTR_OK;
-    };
-    // cross network first (DCN-v2): x_{l+1} = x0 * (W x_l + b) + x_l
-    int xl = 0;
-    for (int l = 0; l < m.n_cross; ++l) {
-        const int out = 3 + (l & 1);
-        if ((rc = add_op(1, l, EPI_CROSS, xl, out, xl)) != CTR_OK) return rc;
-        xl = out;
-    }
-    // MLP on x0
-    int a = 0;
-    for (int l = 0; l < m.n_hidden; ++l) {
-        const GemmLayer& L = dm.mlp[l];
-        const bool last = l == m.n_hidden - 1;
-        const bool fuse_head = last && L.Npad == L.BN;      // whole layer width inside one tile
-        const int out = 1 + (l & 1);
-        if ((rc = add_op(0, l, fuse_head ? EPI_HEAD : EPI_RELU, a, out, -1)) != CTR_OK) return rc;
-        a = out;
-    }
-    return CTR_OK;
+    return build_chains(e, dm, s);
 }
 
 int32_t init_slot_common(Slot& s, int dev, cudaStream_t stream /*nullptr -> create*/) {
@@ -550,24 +574,21 @@ void launch_gather(const ModelDesc& m, bool sharded, const GatherParams& gp, int
     }
 }
 
-template <int BN>
-void launch_gemm_pair_bn(int epi, const CUtensorMap& ma, const CUtensorMap& mw, const GemmParams& gp, int grid, cudaStream_t st) {
-    const size_t smem = GemmPairCfg<BN>::kSmemBytes;
-    switch (epi) {
-        case EPI_RELU: gemm_f16_pair_kernel<BN, EPI_RELU><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
-        case EPI_CROSS: gemm_f16_pair_kernel<BN, EPI_CROSS><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
-        default: gemm_f16_pair_kernel<BN, EPI_HEAD><<<grid, kGemmThreads, smem, st>>>(ma, mw, gp); break;
-    }
+// One chain on `st`: persistent CTA pairs, at most one pair per TPC and per scratch slice.
+int32_t launch_chain(const Chain& c, const Slot& s, int n, float* d_scores, int num_sms, cudaStream_t st, long long* prof = nullptr) {
+    ChainParams p = c.params;
+    p.M = n;
+    p.prof = prof;
+    if (!p.extra_out) p.scores = d_scores;
+    const int tiles = (n + 2 * kBM - 1) / (2 * kBM);
+    const int pairs = std::max(1, std::min(std::min(tiles, num_sms / 2), s.scratch_rows / (2 * kBM)));
+    if (c.BN == 256) tower_chain_kernel<256><<<2 * pairs, kGemmThreads, ChainCfg<256>::kSmemBytes, st>>>(c.maps, p);
+    else tower_chain_kernel<128><<<2 * pairs, kGemmThreads, ChainCfg<128>::kSmemBytes, st>>>(c.maps, p);
+    CUDA_TRY(cudaGetLastError());
+    return CTR_OK;
 }
 
-// One tower layer on `st`: CTA pairs over 256-row tiles, one pair per TPC, persistent.
-void launch_gemm(const GemmLayer& L, int epi, const CUtensorMap& map_a, const GemmParams& p, int rows, int num_sms, cudaStream_t st) {
-    const int tiles = ((rows + 2 * kBM - 1) / (2 * kBM)) * (L.Npad / L.BN);
-    const int grid = 2 * std::max(1, std::min(tiles, num_sms / 2));
-    if (L.BN == 256) launch_gemm_pair_bn<256>(epi, map_a, L.map_w_pair, p, grid, st);
-    else launch_gemm_pair_bn<128>(epi, map_a, L.map_w_pair, p, grid, st);
-}
-
+// Records a CUDA event on the launching stream in front of a stage (stage -2 = end of chunk).
 void mark(ctr_engine* e, Slot& s, int stage) {
     if (!e->timing || !s.time_this || !s.tev || s.sets_recorded >= Slot::kTimeSets || s.cur_mark >= Slot::kTimeMarks) return;
     s.mark_stage[s.cur_mark] = stage;
@@ -575,7 +596,7 @@ void mark(ctr_engine* e, Slot& s, int stage) {
     if (stage == -2) { s.n_marks = s.cur_mark; s.cur_mark = 0; ++s.sets_recorded; s.time_this = false; }
 }
 
-// Scores rows [0, n) of (d_ids, d_wts) into d_scores on s.stream; n <= s.act_rows for tower models.
+// Scores rows [0, n) of (d_ids, d_wts) into d_scores on s.stream; n <= s.x_rows for tower models.
 int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int n, float* d_scores) {
     const ModelDesc& m = e->m;
     DeviceModel& dm = dc.model;
@@ -599,52 +620,11 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
     launch_gather(m, sharded, gp, ggrid, gsmem, st);
     CUDA_TRY(cudaGetLastError());
     e->launches.fetch_add(1, std::memory_order_relaxed);
-    if (m.kind == CTR_MODEL_LR) { mark(e, s, -2); return CTR_OK; }
-
-    const int xl_final = m.n_cross ? 3 + ((m.n_cross - 1) & 1) : -1;
-    bool head_fused = false;
     int li = 0;
-    for (GemmOp& op : s.ops) {
-        const GemmLayer& L = op.layer_kind == 0 ? dm.mlp[op.layer] : dm.cross[op.layer];
-        GemmParams p;
-        memset(&p, 0, sizeof(p));
-        p.M = n; p.N = L.Npad; p.K = L.Kpad; p.bias = L.bias;
-        p.out = s.buf[op.out_buf]; p.ldo = s.ld[op.out_buf];
-        if (op.epi == EPI_CROSS) { p.x0 = s.buf[0]; p.xl = s.buf[op.xl_buf]; p.ldx = s.ld[0]; }
-        if (op.epi == EPI_HEAD) {
-            if (m.kind == CTR_MODEL_DCN_V2) {
-                // x_L part of the head first: extra[b] = w_x . x_L[b]
-                HeadParams hp;
-                memset(&hp, 0, sizeof(hp));
-                hp.n = n; hp.XL = s.buf[xl_final]; hp.ldxl = s.ld[xl_final]; hp.nx = m.d_pad(); hp.w_x = dm.w_out_x;
-                hp.extra_out = s.d_extra;
-                mark(e, s, 100);
-                head_kernel<<<std::min((n + 7) / 8, dm.num_sms * 8), 256, 0, st>>>(hp);
-                CUDA_TRY(cudaGetLastError());
-                e->launches.fetch_add(1, std::memory_order_relaxed);
-                p.extra = s.d_extra;
-            } else {
-                p.wide = s.d_wide;
-            }
-            p.w_out = dm.w_out_h; p.b_out = dm.b_out; p.scores = d_scores;
-            head_fused = true;
-        }
+    for (const Chain& c : s.chains) {
         mark(e, s, ++li);
-        launch_gemm(L, op.epi, op.map_a, p, n, dm.num_sms, st);
-        CUDA_TRY(cudaGetLastError());
-        e->launches.fetch_add(1, std::memory_order_relaxed);
-    }
-    if (!head_fused) {
-        const GemmOp& last = s.ops.back();
-        HeadParams hp;
-        memset(&hp, 0, sizeof(hp));
-        hp.n = n; hp.H = s.buf[last.out_buf]; hp.ldh = s.ld[last.out_buf]; hp.nh = dm.mlp.back().Npad; hp.w_h = dm.w_out_h;
-        if (m.kind == CTR_MODEL_DCN_V2) { hp.XL = s.buf[xl_final]; hp.ldxl = s.ld[xl_final]; hp.nx = m.d_pad(); hp.w_x = dm.w_out_x; }
-        else hp.wide = s.d_wide;
-        hp.b_out = dm.b_out; hp.scores = d_scores;
-        mark(e, s, 100);
-        head_kernel<<<std::min((n + 7) / 8, dm.num_sms * 8), 256, 0, st>>>(hp);
-        CUDA_TRY(cudaGetLastError());
+        int32_t rc = launch_chain(c, s, n, d_scores, dm.num_sms, st);
+        if (rc != CTR_OK) return rc;
         e->launches.fetch_add(1, std::memory_order_relaxed);
     }
     mark(e, s, -2);
@@ -654,7 +634,7 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
 // Scores n candidates (device pointers) on slot s, chunked so activations stay in their buffers.
 int32_t score_on_slot(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int64_t n, float* d_scores) {
     const int F = e->m.F;
-    const int64_t step = e->m.kind == CTR_MODEL_LR ? (int64_t)1 << 30 : s.act_rows;
+    const int64_t step = e->m.kind == CTR_MODEL_LR ? (int64_t)1 << 30 : s.x_rows;
     for (int64_t c0 = 0; c0 < n; c0 += step) {
         const int cnt = (int)std::min<int64_t>(step, n - c0);
         s.time_this = false;                   // stage timing is for ctr_score_device calls
@@ -877,7 +857,9 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
             if ((rc = build_slot_plan(e, dc, *s, true)) != CTR_OK) return rc;
             dc.worker_slots.push_back(std::move(s));
         }
-        int n_dev_slots = 2;
+        // one stream by default: gather and tower both fill the machine, and a second stream only
+        // interleaves them (+4% throughput, measured) at the price of blurred per-kernel timing
+        int n_dev_slots = 1;
         if (const char* c = getenv("CTR_DEVICE_STREAMS")) { int v = atoi(c); if (v >= 1 && v <= 8) n_dev_slots = v; }
         for (int w = 0; w < n_dev_slots; ++w) {
             std::unique_ptr<Slot> s(new Slot());
@@ -904,7 +886,7 @@ int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out) {
     for (int i = 0; i < CTR_MAX_HIDDEN; ++i) out->hidden[i] = e->m.hidden[i];
     out->n_cross = e->m.n_cross; out->d_padded = e->m.d_pad(); out->num_rows = e->m.V;
     out->table_bytes_per_device = (int64_t)e->devs[0]->model.table_bytes;
-    out->chunk_rows = e->devs[0]->dev_slots.empty() ? 0 : e->devs[0]->dev_slots[0]->act_rows;
+    out->chunk_rows = e->devs[0]->dev_slots.empty() ? 0 : e->devs[0]->dev_slots[0]->x_rows;
     return CTR_OK;
 }
 
@@ -1021,7 +1003,7 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
     const float* wts = static_cast<const float*>(d_wts);
     float* scores = static_cast<float*>(d_scores);
     const int n_slots = (int)dc.dev_slots.size();
-    const int64_t step = e->m.kind == CTR_MODEL_LR ? n_cand : dc.dev_slots[0]->act_rows;
+    const int64_t step = e->m.kind == CTR_MODEL_LR ? n_cand : dc.dev_slots[0]->x_rows;
     const int64_t n_chunks = (n_cand + step - 1) / step;
     const int used = (int)std::min<int64_t>(n_slots, n_chunks);
     // fork: the engine's streams start after whatever the caller queued on `origin`
@@ -1130,35 +1112,42 @@ int32_t ctr_debug_gemm(ctr_engine* e, int32_t device_index, const float* A, cons
     CUDA_TRY(cudaMemcpyAsync(dA32, A, (size_t)M * K * sizeof(float), cudaMemcpyHostToDevice, st));
     convert_pad_f16_kernel<<<1024, 256, 0, st>>>(dA32, M, K, dA, Mpad, L.Kpad);
     CUDA_TRY(cudaGetLastError());
-    CUtensorMap map_a;
-    if ((rc = make_map_f16(&map_a, dA, (uint64_t)Mpad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, kBM)) != CTR_OK) return rc;
-    GemmParams p;
-    memset(&p, 0, sizeof(p));
-    p.M = M; p.N = L.Npad; p.K = L.Kpad; p.bias = L.bias; p.out = dO; p.ldo = L.Npad;
+    Chain c;
+    memset(&c.params, 0, sizeof(c.params));
+    c.BN = (L.Npad % 256 == 0) ? 256 : 128;
+    c.n_layers = 1;
+    if ((rc = make_map_f16(&c.maps.a[0], dA, (uint64_t)Mpad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, kBM)) != CTR_OK) return rc;
+    if ((rc = make_map_f16(&c.maps.w[0], L.W, (uint64_t)L.Npad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, c.BN / 2)) != CTR_OK) return rc;
+    ChainLayer& cl = c.params.layer[0];
+    cl.N = L.Npad; cl.K = L.Kpad; cl.epi = EPI_RELU; cl.a_global = 1; cl.bias = L.bias; cl.a_ptr = dA; cl.lda = L.Kpad;
+    cl.out = dO; cl.ldo = L.Npad; cl.out_global = 1;
+    c.params.n_layers = 1;
+    c.params.extra_out = nullptr;
+    Slot fake;
+    fake.scratch_rows = Mpad;
     long long* d_prof = nullptr;
     const bool prof = getenv("CTR_GEMM_PROF") != nullptr;
     if (prof) {
         CUDA_TRY(cudaMalloc(&d_prof, (size_t)num_sms * 8 * sizeof(long long)));
         CUDA_TRY(cudaMemsetAsync(d_prof, 0, (size_t)num_sms * 8 * sizeof(long long), st));
-        p.prof = d_prof;
-        launch_gemm(L, EPI_RELU, map_a, p, M, num_sms, st);        // warm-up (cold L2 / descriptors)
+        if ((rc = launch_chain(c, fake, M, nullptr, num_sms, st, d_prof)) != CTR_OK) return rc;     // warm-up
     }
-    launch_gemm(L, EPI_RELU, map_a, p, M, num_sms, st);
-    CUDA_TRY(cudaGetLastError());
+    if ((rc = launch_chain(c, fake, M, nullptr, num_sms, st, d_prof)) != CTR_OK) return rc;
+    e->launches.fetch_add(1, std::memory_order_relaxed);
     if (prof) {
         std::vector<long long> h((size_t)num_sms * 8);
         CUDA_TRY(cudaMemcpyAsync(h.data(), d_prof, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
-        const char* names[7] = {"producer wait empty", "mma wait acc_empty", "mma wait full", "mma issue+commit", "mma loop total", "epi wait acc_full", "epi body"};
-        fprintf(stderr, "[gemm prof] M=%d N=%d K=%d BN=%d (cycles; CTA0 leader / CTA1 peer / CTA2 / mean over leaders)\n", M, N, K, L.BN);
-        for (int i = 0; i < 7; ++i) {
+        const char* names[8] = {"producer wait empty", "mma wait acc_empty", "mma wait full", "mma issue+commit", "mma loop total",
+                                "epi wait acc_full", "epi body", "producer wait layer"};
+        fprintf(stderr, "[chain prof] M=%d N=%d K=%d BN=%d (cycles; CTA0 leader / CTA1 peer / CTA2 / mean over leaders)\n", M, N, K, c.BN);
+        for (int i = 0; i < 8; ++i) {
             double mean = 0; int cnt = 0;
-            for (int c = 0; c < num_sms; c += 2) if (h[c * 8 + 4]) { mean += (double)h[c * 8 + i]; ++cnt; }
+            for (int cta = 0; cta < num_sms; cta += 2) if (h[cta * 8 + 4]) { mean += (double)h[cta * 8 + i]; ++cnt; }
             fprintf(stderr, "  %-22s %10lld %10lld %10lld   mean %.0f\n", names[i], h[i], h[8 + i], h[16 + i], cnt ? mean / cnt : 0.0);
         }
         cudaFree(d_prof);
     }
-    e->launches.fetch_add(1, std::memory_order_relaxed);
     std::vector<__half> h((size_t)M * L.Npad);
     CUDA_TRY(cudaMemcpyAsync(h.data(), dO, h.size() * sizeof(__half), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
@@ -1177,7 +1166,7 @@ int32_t ctr_debug_gather(ctr_engine* e, int32_t device_index, const int64_t* ids
     std::lock_guard<std::mutex> lk(dc.dev_mu);
     Slot& s = *dc.dev_slots[0];
     const ModelDesc& m = e->m;
-    if (n > s.act_rows || n > s.cap) return fail(CTR_ERR_CAPACITY, "ctr_debug_gather: n exceeds the chunk size");
+    if ((e->m.kind != CTR_MODEL_LR && n > s.x_rows) || n > s.cap) return fail(CTR_ERR_CAPACITY, "ctr_debug_gather: n exceeds the chunk size");
     CUDA_TRY(cudaSetDevice(s.dev));
     CUDA_TRY(cudaMemcpyAsync(s.d_ids, ids, (size_t)n * m.F * sizeof(int64_t), cudaMemcpyHostToDevice, s.stream));
     CUDA_TRY(cudaMemcpyAsync(s.d_wts, wts, (size_t)n * m.F * sizeof(float), cudaMemcpyHostToDevice, s.stream));
@@ -1274,7 +1263,7 @@ extern "C" int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, 
     // A slot whose buffers are slices of the fixed array; nothing in it is allocated or freed.
     Slot s;
     s.dev = dm.dev; s.stream = st; s.owns_stream = false;
-    s.cap = kStaticMaxCandidates; s.act_rows = kStaticMaxCandidates;
+    s.cap = kStaticMaxCandidates; s.x_rows = kStaticMaxCandidates; s.scratch_rows = kStaticMaxCandidates;
     unsigned char* p = base;
     s.buf[0] = reinterpret_cast<__half*>(p); p += kStaticXBytes;
     s.buf[1] = reinterpret_cast<__half*>(p); p += kStaticHBytes;
@@ -1288,31 +1277,9 @@ extern "C" int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, 
     for (auto& L : dm.mlp) maxn = std::max(maxn, L.Npad);
     s.ld[0] = m.d_pad(); s.ld[1] = maxn; s.ld[2] = maxn; s.ld[3] = m.d_pad(); s.ld[4] = m.d_pad();
     if (m.kind != CTR_MODEL_LR) {
-        auto add_op = [&](int kind, int layer, int epi, int a, int out, int xl) -> int32_t {
-            GemmOp op;
-            op.layer_kind = kind; op.layer = layer; op.epi = epi; op.a_buf = a; op.out_buf = out; op.xl_buf = xl;
-            const GemmLayer& L = kind == 0 ? dm.mlp[layer] : dm.cross[layer];
-            int32_t r = make_map_f16(&op.map_a, s.buf[a], (uint64_t)kStaticMaxCandidates, (uint64_t)L.Kpad, (uint64_t)s.ld[a], kBM);
-            if (r != CTR_OK) return r;
-            s.ops.push_back(op);
-            return CTR_OK;
-        };
-        int xl = 0;
-        for (int l = 0; l < m.n_cross; ++l) {
-            const int out = 3 + (l & 1);
-            if ((rc = add_op(1, l, EPI_CROSS, xl, out, xl)) != CTR_OK) return rc;
-            xl = out;
-        }
-        int a = 0;
-        for (int l = 0; l < m.n_hidden; ++l) {
-            const GemmLayer& L = dm.mlp[l];
-            const bool fuse_head = l == m.n_hidden - 1 && L.Npad == L.BN;
-            const int out = 1 + (l & 1);
-            if ((rc = add_op(0, l, fuse_head ? EPI_HEAD : EPI_RELU, a, out, -1)) != CTR_OK) return rc;
-            a = out;
-        }
+        if ((rc = build_chains(e, dm, s)) != CTR_OK) return rc;      // tensor maps over the slices (host-side encode only)
         // the previous call (any engine, any model) may have left anything here: clear what must be zero
-        const size_t x_bytes = (size_t)round_up((int)n_cand, kBM) * s.ld[0] * sizeof(__half);
+        const size_t x_bytes = (size_t)round_up((int)n_cand, 2 * kBM) * s.ld[0] * sizeof(__half);
         CUDA_TRY(cudaMemsetAsync(s.buf[0], 0, x_bytes, st));
     }
     CUDA_TRY(cudaMemsetAsync(s.d_err, 0, sizeof(int32_t), st));

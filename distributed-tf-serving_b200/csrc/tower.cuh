@@ -1,0 +1,394 @@
+// tower.cuh -- the dense tower as ONE persistent tcgen05 / TMEM / TMA kernel per chain of layers
+// (north star (c)).  A chain is a sequence of layers in which each layer's output is the next
+// layer's input: the MLP of Wide&Deep / DeepFM / DCN-v2, or DCN-v2's cross network.
+//
+//     layer:  OUT[m, n] = epi( sum_k A[m, k] * W[n, k] + bias[n] )        A, W: half, K-major
+//       EPI_RELU      OUT = max(acc + b, 0)                       -> half, next layer's A
+//       EPI_CROSS     OUT = X0[m,n] * (acc + b) + A[m,n]          -> half, next layer's A   (DCN-v2 cross)
+//       EPI_HEAD      dot += sum_n max(acc + b, 0) * w_out[n]     (last MLP layer + the 1-wide output layer)
+//       EPI_CROSS_DOT dot += sum_n (X0 * (acc + b) + A)[n] * w_out[n]   (last cross layer: the x_L part of the head)
+//     after a dot layer:  scores[m] = sigmoid(dot + b_out + wide[m] + extra_in[m])   or   extra_out[m] = dot
+//
+// Why one kernel per chain.  Measured with cycle counters on B200: a single 18944 x 1024 x 640
+// layer spends ~15 us in its MMA loop but ~29 us from event to event -- launch, prologue (barrier
+// init, TMEM allocation, cluster sync, descriptor fetch), pipeline ramp and the last epilogue cost
+// 11-14 us per launch, three times per chunk.  Here a CTA pair owns a 256-row tile of candidates
+// and walks it through every layer of the chain; the intermediate activations of that tile go to
+// a small per-pair scratch that never leaves L2, the accumulators stay double-buffered across
+// layer boundaries, and the W tiles of the next layer are already in flight while the previous
+// layer's epilogue drains.
+//
+// Structure (CTAs paired into clusters of 2 = one TPC, persistent, 384 threads per CTA):
+//   warp 0     TMA producer: cp.async.bulk.tensor 2-D loads (128-byte swizzle) of this CTA's 128
+//              rows of A and its HALF of the W tile into a shared-memory ring (mbarrier paced);
+//              both CTAs' loads complete on the leader's barrier
+//   warp 1     MMA issuer (leader CTA): one thread issues tcgen05.mma.cta_group::2 (M=256, N=BN,
+//              K=16, f16 -> f32), accumulators in the TMEM of both SMs; tcgen05.commit multicasts
+//              "stage free" / "accumulator ready" to both CTAs
+//   warp 2     TMEM allocator (2 accumulators x BN columns: tile i's epilogue overlaps tile i+1's MMAs)
+//   warps 4-11 epilogue: tcgen05.ld -> registers -> bias / activation -> XOR-swizzled warp-private
+//              staging in shared memory -> row-major 16-byte stores (a thread owns a ROW in TMEM;
+//              storing straight from registers costs 32 L1 wavefronts per instruction and made the
+//              first version epilogue-bound: 7.5k cycles per tile against 5.1k of MMA)
+// Every mbarrier wait is bounded (2 s, then trap): a descriptor or phase bug becomes a CUDA error.
+//
+// Roofline: tensor pipe.  Per K block a CTA pulls 16 KB (A) + BN/2 * 128 B (W half) from L2
+// -- with 1-CTA 128x256 tiles (48 KB per K block) the kernel measured ~10 TB/s of L2->SM
+// traffic, i.e. it was L2-bandwidth bound.
+#pragma once
+#include "common.cuh"
+
+namespace ctr {
+
+constexpr int kGemmThreads = 384;       // 4 control warps + 8 epilogue warps
+constexpr int kBM = 128;                // rows per CTA; a pair covers 2 * kBM
+constexpr int kBK = 64;                 // 64 halfs = one 128-byte swizzle span
+constexpr int kMaxChain = 4;
+
+enum GemmEpilogue { EPI_RELU = 0, EPI_CROSS = 1, EPI_HEAD = 2, EPI_CROSS_DOT = 3 };
+
+struct ChainLayer {
+    int32_t N, K;              // padded output / reduction widths (N multiple of BN, K of 64)
+    int32_t epi;
+    int32_t a_global;          // A rows addressed by candidate row (first layer) or by pair-scratch row
+    const float* bias;         // [N]
+    const __half* a_ptr;       // the A operand as a plain pointer (EPI_CROSS* reads x_l from it)
+    int32_t lda;
+    __half* out;               // pair-scratch output [n_pairs * 256, ldo] (EPI_RELU / EPI_CROSS)
+    int32_t ldo;
+    int32_t out_global;        // test hook: store by candidate row instead of pair-scratch row
+    const float* w_out;        // [N] (dot epilogues)
+};
+
+struct ChainParams {
+    int32_t M;                 // candidates in this launch
+    int32_t n_layers;
+    ChainLayer layer[kMaxChain];
+    const __half* x0;          // [M, ldx0] gathered activations (EPI_CROSS*)
+    int32_t ldx0;
+    const float* wide;         // [M] or nullptr
+    const float* extra_in;     // [M] or nullptr
+    float b_out;
+    float* scores;             // [M]: sigmoid(dot + ...) after a dot layer, or nullptr
+    float* extra_out;          // [M]: raw dot after a dot layer, or nullptr
+    long long* prof;           // bring-up instrumentation (nullptr in production)
+};
+
+struct ChainMaps {
+    CUtensorMap a[kMaxChain];
+    CUtensorMap w[kMaxChain];
+};
+
+template <int BN>
+struct ChainCfg {
+    static constexpr int kABytes = kBM * kBK * 2;                 // 16 KB: this CTA's 128 rows
+    static constexpr int kBBytes = (BN / 2) * kBK * 2;            // 16 KB / 8 KB: this CTA's half of the W tile
+    static constexpr int kStageBytes = kABytes + kBBytes;
+    static constexpr int kStages = BN == 256 ? 5 : 6;
+    static constexpr int kTmemCols = 2 * BN;
+    static constexpr int kStoreStageBytes = 8 * 4096;             // 8 epilogue warps x (32 rows x 128 B)
+    static constexpr int kSmemBytes = kStages * kStageBytes + kStoreStageBytes + 1024 + 256;
+};
+
+// Drains one half (BN/2 columns) of a 128-row accumulator tile for the calling warp's 32 rows.
+//   grow_base: candidate row of the warp's first row (guards, x0, wide); srow_base: scratch row.
+template <int BN>
+__device__ __forceinline__ void epilogue_half_tile(const ChainParams& p, const ChainLayer& L, uint32_t taddr, int grow_base,
+                                                   int srow_base, int lane, int n0, float& dot, uint4* stage) {
+    constexpr int kChunks = (BN / 2) / 32;
+    static_assert(kChunks % 2 == 0, "two 32-column chunks per staging round");
+    const int epi = L.epi;
+    const bool cross = epi == EPI_CROSS || epi == EPI_CROSS_DOT;
+    const bool dot_epi = epi == EPI_HEAD || epi == EPI_CROSS_DOT;
+    const int grow = grow_base + lane;
+    const bool row_ok = grow < p.M;
+    uint32_t r[2][32];
+    tmem_ld32(taddr, r[0]);
+#pragma unroll
+    for (int c = 0; c < kChunks; ++c) {
+        const int col0 = n0 + c * 32;
+        float4 bv[8];                                          // same address in every lane: broadcast, L1-resident
+        const float4* bias4 = reinterpret_cast<const float4*>(L.bias + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) bv[j] = __ldg(bias4 + j);
+        tmem_ld_wait();                                        // chunk c has landed in r[c & 1]
+        if (c + 1 < kChunks) tmem_ld32(taddr + (c + 1) * 32, r[(c + 1) & 1]);   // overlaps the math below
+        const uint32_t* rc = r[c & 1];
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            v[4 * j + 0] = __uint_as_float(rc[4 * j + 0]) + bv[j].x;
+            v[4 * j + 1] = __uint_as_float(rc[4 * j + 1]) + bv[j].y;
+            v[4 * j + 2] = __uint_as_float(rc[4 * j + 2]) + bv[j].z;
+            v[4 * j + 3] = __uint_as_float(rc[4 * j + 3]) + bv[j].w;
+        }
+        if (!cross) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
+        } else if (row_ok) {                                   // x0 * (acc + b) + x_l
+            const int arow = L.a_global ? grow : srow_base + lane;
+            const uint4* x0p = reinterpret_cast<const uint4*>(p.x0 + (size_t)grow * p.ldx0 + col0);
+            const uint4* xlp = reinterpret_cast<const uint4*>(L.a_ptr + (size_t)arow * L.lda + col0);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint4 a = __ldg(x0p + j), b = *(xlp + j);
+                const __half2* ah = reinterpret_cast<const __half2*>(&a);
+                const __half2* bh = reinterpret_cast<const __half2*>(&b);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float2 af = __half22float2(ah[e]), bf = __half22float2(bh[e]);
+                    v[8 * j + 2 * e + 0] = fmaf(af.x, v[8 * j + 2 * e + 0], bf.x);
+                    v[8 * j + 2 * e + 1] = fmaf(af.y, v[8 * j + 2 * e + 1], bf.y);
+                }
+            }
+        }
+        if (dot_epi) {
+            const float4* w4 = reinterpret_cast<const float4*>(L.w_out + col0);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float4 wv = __ldg(w4 + j);
+                dot = fmaf(v[4 * j + 0], wv.x, dot);
+                dot = fmaf(v[4 * j + 1], wv.y, dot);
+                dot = fmaf(v[4 * j + 2], wv.z, dot);
+                dot = fmaf(v[4 * j + 3], wv.w, dot);
+            }
+        } else {
+            // this thread's 32 columns -> 4 x 16 B into its row of the staging block (swizzled: conflict-free)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                __half2 h[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[8 * j + 2 * e], v[8 * j + 2 * e + 1]);
+                const int lc = (c & 1) * 4 + j;
+                stage[lane * 8 + (lc ^ (lane & 7))] = *reinterpret_cast<const uint4*>(h);
+            }
+            if (c & 1) {
+                __syncwarp();
+                const int colbase = n0 + (c - 1) * 32;               // first of the 64 staged columns
+                const int cc = lane & 7;
+#pragma unroll
+                for (int it = 0; it < 8; ++it) {
+                    const int rr = it * 4 + (lane >> 3);
+                    const uint4 val = stage[rr * 8 + (cc ^ (rr & 7))];
+                    if (grow_base + rr < p.M)
+                        *reinterpret_cast<uint4*>(L.out + (size_t)((L.out_global ? grow_base : srow_base) + rr) * L.ldo + colbase + cc * 8) = val;
+                }
+                __syncwarp();
+            }
+        }
+    }
+}
+
+template <int BN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainParams p) {
+    using Cfg = ChainCfg<BN>;
+    constexpr int kStages = Cfg::kStages;
+    extern __shared__ uint8_t smem_raw[];
+    // 128-byte swizzle needs 1024-byte aligned stage buffers
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + kStages * Cfg::kABytes;
+    uint8_t* store_stage = smem + kStages * Cfg::kStageBytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(store_stage + Cfg::kStoreStageBytes);
+    uint64_t* full_bar = bars;                     // [kStages] used in the leader: both CTAs' TMA -> MMA
+    uint64_t* empty_bar = bars + kStages;          // [kStages] in each CTA: MMA -> that CTA's producer
+    uint64_t* acc_full = bars + 2 * kStages;       // [2] in each CTA: MMA -> that CTA's epilogue
+    uint64_t* acc_empty = bars + 2 * kStages + 2;  // [2] used in the leader: both CTAs' epilogues -> MMA
+    uint64_t* layer_done = bars + 2 * kStages + 4; // [1] in each CTA: epilogue (layer l stored) -> producer (layer l+1 A loads)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 5);
+    __shared__ float dot_part[2 * kBM];            // high-column-half partial dots, double-buffered
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const int pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
+    const int tiles_m = (p.M + 2 * kBM - 1) / (2 * kBM);            // 256-row tiles of candidates
+    const int nl = p.n_layers;
+
+    if (warp == 0 && lane == 0) {
+        for (int l = 0; l < nl; ++l) { tma_prefetch_desc(&maps.a[l]); tma_prefetch_desc(&maps.w[l]); }
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 16); }
+        mbar_init(layer_done, 8);
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
+        tmem_relinquish_pair();
+    }
+    tc_fence_before();
+    cluster_sync_all();                              // barriers of both CTAs are initialised before anyone signals them
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0, ld_ph = 0;
+            long long w_empty = 0, w_layer = 0;
+            for (int t = pair_id; t < tiles_m; t += n_pairs) {
+                for (int l = 0; l < nl; ++l) {
+                    const ChainLayer& L = p.layer[l];
+                    const int a_row = (L.a_global ? t : pair_id) * 2 * kBM + (int)rank * kBM;
+                    const int tiles_n = L.N / BN, k_blocks = L.K / kBK;
+                    for (int nt = 0; nt < tiles_n; ++nt) {
+                        const int w_row = nt * BN + (int)rank * (BN / 2);
+                        for (int kb = 0; kb < k_blocks; ++kb) {
+                            long long c0 = p.prof ? clock64() : 0;
+                            mbar_wait(&empty_bar[s], ph ^ 1);
+                            if (p.prof) w_empty += clock64() - c0;
+                            const uint32_t lead_full = map_to_cta(smem_u32(&full_bar[s]), 0);
+                            if (leader) mbar_expect_tx(&full_bar[s], 2 * Cfg::kStageBytes);      // bytes of both CTAs
+                            tma_load_2d_pair(smem_b + s * Cfg::kBBytes, &maps.w[l], kb * kBK, w_row, lead_full);
+                            if (l > 0 && nt == 0 && kb == 0) {
+                                // A of this layer is what this CTA's epilogue stored for the previous layer:
+                                // wait until all 8 epilogue warps have published it (the W tile above is
+                                // already in flight)
+                                c0 = p.prof ? clock64() : 0;
+                                mbar_wait(layer_done, ld_ph);
+                                ld_ph ^= 1;
+                                if (p.prof) w_layer += clock64() - c0;
+                            }
+                            tma_load_2d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], kb * kBK, a_row, lead_full);
+                            if (!leader) mbar_arrive_cluster(lead_full);
+                            if (++s == kStages) { s = 0; ph ^= 1; }
+                        }
+                    }
+                }
+            }
+            if (p.prof) { p.prof[blockIdx.x * 8 + 0] = w_empty; p.prof[blockIdx.x * 8 + 7] = w_layer; }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer (leader CTA only) =====================
+        if (leader && lane == 0) {
+            constexpr uint32_t idesc = make_idesc_f16(2 * kBM, BN, /*f16*/ 0);
+            int s = 0; uint32_t ph = 0;
+            int lt = 0;
+            long long w_acc = 0, w_full = 0, t_issue = 0;
+            const long long k0 = p.prof ? clock64() : 0;
+            for (int t = pair_id; t < tiles_m; t += n_pairs) {
+                for (int l = 0; l < nl; ++l) {
+                    const int tiles_n = p.layer[l].N / BN, k_blocks = p.layer[l].K / kBK;
+                    for (int nt = 0; nt < tiles_n; ++nt, ++lt) {
+                        const int acc = lt & 1;
+                        long long c0 = p.prof ? clock64() : 0;
+                        mbar_wait(&acc_empty[acc], ((lt >> 1) & 1) ^ 1);      // both CTAs' epilogues drained it
+                        if (p.prof) w_acc += clock64() - c0;
+                        tc_fence_after();
+                        const uint32_t d_tmem = tmem_base + acc * BN;
+                        for (int kb = 0; kb < k_blocks; ++kb) {
+                            c0 = p.prof ? clock64() : 0;
+                            mbar_wait(&full_bar[s], ph);
+                            const long long c1 = p.prof ? clock64() : 0;
+                            tc_fence_after();
+                            const uint32_t a_addr = smem_u32(smem_a + s * Cfg::kABytes);
+                            const uint32_t b_addr = smem_u32(smem_b + s * Cfg::kBBytes);
+#pragma unroll
+                            for (int k = 0; k < kBK / 16; ++k) {
+                                // advancing K by 16 halfs = 32 bytes inside the 128-byte swizzle span
+                                const uint64_t da = make_sw128_kmajor_desc(a_addr + k * 32);
+                                const uint64_t db = make_sw128_kmajor_desc(b_addr + k * 32);
+                                umma_f16_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                            }
+                            umma_commit_pair(&empty_bar[s]);                  // stage free in both CTAs
+                            if (p.prof) { w_full += c1 - c0; t_issue += clock64() - c1; }
+                            if (++s == kStages) { s = 0; ph ^= 1; }
+                        }
+                        umma_commit_pair(&acc_full[acc]);                     // accumulator ready in both CTAs
+                    }
+                }
+            }
+            if (p.prof) {
+                p.prof[blockIdx.x * 8 + 1] = w_acc; p.prof[blockIdx.x * 8 + 2] = w_full; p.prof[blockIdx.x * 8 + 3] = t_issue;
+                p.prof[blockIdx.x * 8 + 4] = clock64() - k0;
+            }
+        }
+    } else if (warp >= 4) {
+        // ===================== epilogue (8 warps, both CTAs, own 128 rows) =====================
+        // A warp may only touch the TMEM lanes of its sub-partition (warp % 4); two warps share a
+        // sub-partition and split the tile's columns in halves.
+        const int sub = warp & 3;
+        const int half = (warp - 4) >> 2;
+        constexpr int kHalfCols = BN / 2;
+        uint4* stage = reinterpret_cast<uint4*>(store_stage + (warp - 4) * 4096);
+        int lt = 0, dot_round = 0;
+        long long w_accfull = 0, t_epi = 0;
+        for (int t = pair_id; t < tiles_m; t += n_pairs) {
+            const int grow_base = t * 2 * kBM + (int)rank * kBM + sub * 32;          // candidate rows
+            const int srow_base = pair_id * 2 * kBM + (int)rank * kBM + sub * 32;    // pair-scratch rows
+            for (int l = 0; l < nl; ++l) {
+                const ChainLayer& L = p.layer[l];
+                const int tiles_n = L.N / BN;
+                const bool dot_epi = L.epi == EPI_HEAD || L.epi == EPI_CROSS_DOT;
+                float dot = 0.f;
+                for (int nt = 0; nt < tiles_n; ++nt, ++lt) {
+                    const int acc = lt & 1;
+                    const long long c0 = p.prof ? clock64() : 0;
+                    mbar_wait(&acc_full[acc], (lt >> 1) & 1);
+                    const long long c1 = p.prof ? clock64() : 0;
+                    tc_fence_after();
+                    const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN + half * kHalfCols;
+                    epilogue_half_tile<BN>(p, L, taddr, grow_base, srow_base, lane, nt * BN + half * kHalfCols, dot, stage);
+                    // TMEM reads of this accumulator are done: hand it back to the MMA warp (in the leader)
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive_cluster(map_to_cta(smem_u32(&acc_empty[acc]), 0));
+                    if (p.prof) { w_accfull += c1 - c0; t_epi += clock64() - c1; }
+                }
+                if (dot_epi) {
+                    // the two column halves of a row live in two warps: combine in a fixed order (low + high)
+                    const int buf = dot_round & 1;
+                    ++dot_round;
+                    if (half == 1) dot_part[buf * kBM + sub * 32 + lane] = dot;
+                    asm volatile("bar.sync %0, 64;" ::"r"(1 + sub) : "memory");
+                    const int grow = grow_base + lane;
+                    if (half == 0 && grow < p.M) {
+                        float z = dot + dot_part[buf * kBM + sub * 32 + lane];
+                        if (p.extra_out) p.extra_out[grow] = z;
+                        if (p.scores) {
+                            z += p.b_out;
+                            if (p.wide) z += p.wide[grow];
+                            if (p.extra_in) z += p.extra_in[grow];
+                            p.scores[grow] = sigmoidf_fast(z);
+                        }
+                    }
+                } else if (l + 1 < nl) {
+                    // this layer's rows are stored: make them visible to the TMA (async proxy) reads of
+                    // the next layer, then tell this CTA's producer
+                    asm volatile("fence.proxy.async;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(layer_done);
+                }
+            }
+        }
+        if (p.prof && warp == 4 && lane == 0) { p.prof[blockIdx.x * 8 + 5] = w_accfull; p.prof[blockIdx.x * 8 + 6] = t_epi; }
+    }
+
+    // neither CTA may leave (or free TMEM) while its partner can still touch its shared memory / TMEM
+    tc_fence_before();
+    cluster_sync_all();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+    }
+}
+
+// ------------------------------------------------------------------ small companions
+// fp32 [rows, cols] -> half [rows_pad, cols_pad], zero padded (tower weights at load time)
+__global__ void convert_pad_f16_kernel(const float* src, int rows, int cols, __half* dst, int rows_pad, int cols_pad) {
+    const int64_t total = (int64_t)rows_pad * cols_pad;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(i / cols_pad), c = (int)(i % cols_pad);
+        dst[i] = __float2half_rn((r < rows && c < cols) ? src[(int64_t)r * cols + c] : 0.f);
+    }
+}
+
+__global__ void half_to_float_kernel(const __half* src, int64_t rows, int cols, int ld, float* dst) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < rows * cols; i += (int64_t)gridDim.x * blockDim.x)
+        dst[i] = __half2float(src[(i / cols) * ld + (i % cols)]);
+}
+
+}  // namespace ctr

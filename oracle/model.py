@@ -321,10 +321,10 @@ def forward_logits(w: Weights, ids, wts, mode: str = "fp64") -> np.ndarray:
 
     if s.kind == DCN_V2:
         xl = x0
-        for W, b in w.cross:
+        for ci, (W, b) in enumerate(w.cross):
             y = dense(xl, W, b, relu=False)
             xl = x0 * y + xl
-            if mode == "f16":
+            if mode == "f16" and ci != len(w.cross) - 1:     # the last x_L feeds the head in fp32
                 xl = q(xl.astype(np.float32)).astype(ft)
         feat = np.concatenate([xl, h], axis=1)
     else:
@@ -335,13 +335,10 @@ def forward_logits(w: Weights, ids, wts, mode: str = "fp64") -> np.ndarray:
 
 
 def head_is_fused(spec: ModelSpec) -> bool:
-    """Kernel-contract detail for the "f16" mode: when the last hidden layer fits one GEMM tile
-    (width padded to 128 is 128 or 256) the CUDA path applies the output layer to the fp32
-    accumulators, so that layer's activations are never rounded to half."""
-    if not spec.hidden:
-        return False
-    npad = -(-spec.hidden[-1] // 128) * 128
-    return npad in (128, 256)
+    """Kernel-contract detail for the "f16" mode: the CUDA path applies the output layer to the
+    fp32 accumulators of the last hidden layer (and of the last cross layer), so those
+    activations are never rounded to half."""
+    return bool(spec.hidden)
 
 
 def sigmoid(z: np.ndarray) -> np.ndarray:
