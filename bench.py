@@ -140,6 +140,7 @@ def run_reference(args, rank, world):
     an external TF-Serving, neither present on this image) with all host threads."""
     if rank != 0:
         return
+    os.environ.pop("OMP_NUM_THREADS", None)        # torchrun pins it to 1; the reference arm may use every host core
     tmp = tempfile.mkdtemp(prefix="ctr_bench_")
     path = os.path.join(tmp, "wd.ctrw")
     write_model(path, args.rows_per_field)
