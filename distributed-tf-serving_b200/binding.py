@@ -23,7 +23,8 @@ EXPORTS = ["ctr_engine_create", "ctr_engine_destroy", "ctr_engine_load_weights",
            "ctr_predict_async", "ctr_wait", "ctr_predict", "ctr_alloc_pinned", "ctr_free_pinned",
            "ctr_score_device", "ctr_partition_bounds", "ctr_last_error", "ctr_abi_version",
            "ctr_engine_launch_count", "ctr_engine_set_timing", "ctr_engine_stage_ms", "ctr_debug_read_rows",
-           "ctr_debug_gemm", "ctr_debug_gather", "ctr_score_device_static"]
+           "ctr_debug_gemm", "ctr_debug_gather", "ctr_score_device_static", "ctr_predict_sorted", "ctr_predict_wire",
+           "ctr_wire_parse_request", "ctr_wire_build_response", "ctr_predict_shared_async"]
 
 
 class CtrConfig(C.Structure):
@@ -66,11 +67,16 @@ def load_library() -> C.CDLL:
     lib.ctr_engine_load_weights.argtypes = [vp, C.c_char_p]
     lib.ctr_engine_model_info.argtypes = [vp, C.POINTER(CtrModelInfo)]
     lib.ctr_predict_async.argtypes = [vp, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
+    lib.ctr_predict_shared_async.argtypes = [vp, vp, vp, i32, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
     lib.ctr_wait.argtypes = [vp, i64, i32]
     lib.ctr_predict.argtypes = [vp, vp, vp, i64, vp]
     lib.ctr_alloc_pinned.argtypes = [vp, i64, C.POINTER(vp)]
     lib.ctr_free_pinned.argtypes = [vp, vp]
     lib.ctr_score_device.argtypes = [vp, i32, vp, vp, i64, vp, vp]
+    lib.ctr_predict_sorted.argtypes = [vp, vp, vp, i64, vp, vp]
+    lib.ctr_predict_wire.argtypes = [vp, vp, i64, vp, i64, C.POINTER(i64)]
+    lib.ctr_wire_parse_request.argtypes = [vp, i64, i32, vp, vp, i64, C.POINTER(i64)]
+    lib.ctr_wire_build_response.argtypes = [vp, i64, vp, i64, C.POINTER(i64)]
     lib.ctr_score_device_static.argtypes = [vp, i32, vp, vp, i64, vp, vp]
     lib.ctr_partition_bounds.argtypes = [i64, i32, vp, vp]
     lib.ctr_last_error.restype = C.c_char_p
@@ -97,6 +103,29 @@ def partition_bounds(n: int, part_num: int):
     e = np.zeros(max(part_num, 1), np.int64)
     _check(load_library().ctr_partition_bounds(n, part_num, b.ctypes.data, e.ctypes.data))
     return list(zip(b.tolist(), e.tolist()))
+
+
+def wire_parse_request(request: bytes, field_num: int):
+    """PredictRequest bytes -> (ids [n, F] int64, wts [n, F] float32); host only."""
+    lib = load_library()
+    n = C.c_int64(0)
+    cap = max(len(request), 16)
+    ids = np.empty(cap, np.int64)
+    wts = np.empty(cap, np.float32)
+    _check(lib.ctr_wire_parse_request(request, len(request), field_num, ids.ctypes.data, wts.ctypes.data, cap, C.byref(n)))
+    m = n.value * field_num
+    return ids[:m].reshape(n.value, field_num).copy(), wts[:m].reshape(n.value, field_num).copy()
+
+
+def wire_build_response(scores: np.ndarray) -> bytes:
+    """scores -> PredictResponse bytes (outputs["prediction_node"], DT_FLOAT [n,1]); host only."""
+    lib = load_library()
+    s = np.ascontiguousarray(scores, np.float32)
+    need = C.c_int64(0)
+    cap = 4 * s.size + 128
+    buf = C.create_string_buffer(cap)
+    _check(lib.ctr_wire_build_response(s.ctypes.data, s.size, buf, cap, C.byref(need)))
+    return buf.raw[:need.value]
 
 
 class PinnedBuffer:
@@ -182,17 +211,58 @@ class Engine:
         self._keep[t.value] = (ids, wts, out)
         return t.value, out
 
+    def predict_shared_async(self, ctx_ids, ctx_wts, cand_ids, cand_wts, out: Optional[np.ndarray] = None):
+        """Shared-context request: the first len(ctx_ids) fields of every candidate given once."""
+        ctx_ids = np.ascontiguousarray(ctx_ids, np.int64)
+        ctx_wts = np.ascontiguousarray(ctx_wts, np.float32)
+        cand_ids = np.asarray(cand_ids)
+        cand_wts = np.asarray(cand_wts)
+        fk = self.num_fields - ctx_ids.size
+        if cand_ids.dtype != np.int64 or cand_wts.dtype != np.float32 or not (cand_ids.flags.c_contiguous and cand_wts.flags.c_contiguous):
+            raise TypeError("cand_ids must be C-contiguous int64 and cand_wts C-contiguous float32")
+        if fk < 1 or cand_ids.size % fk or cand_ids.size != cand_wts.size or ctx_wts.size != ctx_ids.size:
+            raise ValueError("candidate lists need n_cand * %d elements each" % fk)
+        n = cand_ids.size // fk
+        if out is None:
+            out = np.empty(n, np.float32)
+        t = C.c_int64()
+        _check(self.lib.ctr_predict_shared_async(self.handle, ctx_ids.ctypes.data, ctx_wts.ctypes.data, ctx_ids.size,
+                                                 cand_ids.ctypes.data, cand_wts.ctypes.data, n, out.ctypes.data, None, None, C.byref(t)))
+        self._keep[t.value] = (ctx_ids, ctx_wts, cand_ids, cand_wts, out)
+        return t.value, out
+
     def wait(self, ticket: int, timeout_ms: int = -1) -> np.ndarray:
         rc = self.lib.ctr_wait(self.handle, ticket, timeout_ms)
         if rc == -5:
             raise CtrError(rc, "timed out")
         kept = self._keep.pop(ticket, None)
         _check(rc)
-        return kept[2] if kept else None
+        return kept[-1] if kept else None
 
     def predict(self, ids, wts, out: Optional[np.ndarray] = None) -> np.ndarray:
         t, out = self.predict_async(ids, wts, out)
         return self.wait(t)
+
+    def predict_sorted(self, ids, wts):
+        """processARequest including its sort (DCNClient.java:195): (ascending scores, candidate index of each)."""
+        ids, wts, n = self._check_inputs(ids, wts)
+        out = np.empty(n, np.float32)
+        order = np.empty(n, np.int32)
+        _check(self.lib.ctr_predict_sorted(self.handle, ids.ctypes.data, wts.ctypes.data, n, out.ctypes.data, order.ctypes.data))
+        return out, order
+
+    def predict_wire(self, request: bytes) -> bytes:
+        """Serialised PredictRequest -> serialised PredictResponse (the RPC of DCNClient.java:112)."""
+        need = C.c_int64(0)
+        cap = 64 + len(request)
+        buf = C.create_string_buffer(cap)
+        rc = self.lib.ctr_predict_wire(self.handle, request, len(request), buf, cap, C.byref(need))
+        if rc == -6 and need.value > cap:
+            cap = need.value
+            buf = C.create_string_buffer(cap)
+            rc = self.lib.ctr_predict_wire(self.handle, request, len(request), buf, cap, C.byref(need))
+        _check(rc)
+        return buf.raw[:need.value]
 
     def pinned(self, shape, dtype) -> PinnedBuffer:
         return PinnedBuffer(self, shape, dtype)

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libctr_b200.so")
 HOST_DEMO = os.path.join(HERE, "dcn_client_host")
-SOURCES = ["engine.cu", "common.cuh", "gather.cuh", "tower.cuh", os.path.join("..", "..", "include", "ctr_engine.h")]
+SOURCES = ["engine.cu", "common.cuh", "gather.cuh", "tower.cuh", "sort.cuh", "wire.hpp", os.path.join("..", "..", "include", "ctr_engine.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-Wall,-pthread", "-shared"]

@@ -13,6 +13,8 @@
 #include "common.cuh"
 #include "gather.cuh"
 #include "tower.cuh"
+#include "sort.cuh"
+#include "wire.hpp"
 
 #include <atomic>
 #include <chrono>
@@ -202,6 +204,7 @@ struct Slot {
     int x_rows = 0;            // candidates per launch: rows of X / wide / extra (multiple of 256)
     int scratch_rows = 0;      // rows of the per-pair scratch (resident CTA pairs x 256)
     int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;
+    int64_t* d_cids = nullptr; float* d_cwts = nullptr;     // compact lists of a shared-context request (host slots)
     float* d_wide = nullptr; float* d_extra = nullptr; int32_t* d_err = nullptr;
     __half* buf[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     int ld[5] = {0, 0, 0, 0, 0};
@@ -231,6 +234,9 @@ struct Request {
 struct Task {
     std::shared_ptr<Request> req;
     const int64_t* ids; const float* wts; int64_t n; float* scores;
+    // shared-context request: the first n_ctx fields of every candidate come from one shared list and
+    // ids / wts hold only the remaining F - n_ctx fields per candidate
+    const int64_t* ctx_ids = nullptr; const float* ctx_wts = nullptr; int32_t n_ctx = 0;
     bool stop = false;
 };
 
@@ -241,6 +247,11 @@ struct DeviceCtx {
     std::mutex dev_mu;                                // serialises ctr_score_device enqueues per device
     cudaStream_t main_stream = nullptr;
     cudaEvent_t fork_ev = nullptr;
+    // device sort scratch (ctr_predict_sorted), allocated on first use
+    std::mutex sort_mu;
+    int64_t sort_cap = 0;
+    float* srt_scores = nullptr; float* srt_sorted = nullptr; uint32_t* srt_keys[2] = {nullptr, nullptr};
+    int32_t* srt_idx[2] = {nullptr, nullptr}; uint32_t* srt_counts = nullptr;
     std::deque<Task> queue;
     std::mutex q_mu;
     std::condition_variable q_cv;
@@ -426,7 +437,7 @@ int32_t load_model_on_device(ctr_engine* e, int di, const HostWeights& hw) {
 // ------------------------------------------------------------------ slots
 void free_slot(Slot& s) {
     cudaSetDevice(s.dev);
-    cudaFree(s.d_ids); cudaFree(s.d_wts); cudaFree(s.d_scores); cudaFree(s.d_wide); cudaFree(s.d_extra); cudaFree(s.d_err);
+    cudaFree(s.d_ids); cudaFree(s.d_wts); cudaFree(s.d_scores); cudaFree(s.d_cids); cudaFree(s.d_cwts); cudaFree(s.d_wide); cudaFree(s.d_extra); cudaFree(s.d_err);
     for (auto*& b : s.buf) { cudaFree(b); b = nullptr; }
     cudaFreeHost(s.h_ids); cudaFreeHost(s.h_wts); cudaFreeHost(s.h_scores); cudaFreeHost(s.h_err);
     if (s.tev) {
@@ -511,6 +522,8 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     CUDA_TRY(cudaMalloc(&s.d_err, sizeof(int32_t)));
     CUDA_TRY(cudaMemset(s.d_err, 0, sizeof(int32_t)));
     if (host_staging) {
+        CUDA_TRY(cudaMalloc(&s.d_cids, ((size_t)s.cap * m.F + CTR_MAX_FIELDS) * sizeof(int64_t)));
+        CUDA_TRY(cudaMalloc(&s.d_cwts, ((size_t)s.cap * m.F + CTR_MAX_FIELDS) * sizeof(float)));
         CUDA_TRY(cudaMallocHost(&s.h_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
         CUDA_TRY(cudaMallocHost(&s.h_wts, (size_t)s.cap * m.F * sizeof(float)));
         CUDA_TRY(cudaMallocHost(&s.h_scores, (size_t)s.cap * sizeof(float)));
@@ -614,7 +627,8 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
     if (m.kind == CTR_MODEL_LR) { gp.scores = d_scores; }
     else { gp.X = s.buf[0]; gp.ldx = s.ld[0]; gp.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide; }
     const int n_tiles = (n + kGatherTile - 1) / kGatherTile;
-    const int ggrid = std::max(1, std::min(n_tiles, dm.num_sms * 4));
+    static const int gather_ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : CTR_GATHER_MIN_CTAS; }();
+    const int ggrid = std::max(1, std::min(n_tiles, dm.num_sms * gather_ctas_per_sm));
     const size_t gsmem = (size_t)2 * kGatherTile * m.F * 12;
     mark(e, s, 0);
     launch_gather(m, sharded, gp, ggrid, gsmem, st);
@@ -685,7 +699,8 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
     const ModelDesc& m = e->m;
     auto body = [&]() -> int32_t {
         CUDA_TRY(cudaSetDevice(s.dev));
-        const size_t ib = (size_t)t.n * m.F * sizeof(int64_t), wb = (size_t)t.n * m.F * sizeof(float), sb = (size_t)t.n * sizeof(float);
+        const int Fk = m.F - t.n_ctx;                          // per-candidate fields actually shipped
+        const size_t ib = (size_t)t.n * Fk * sizeof(int64_t), wb = (size_t)t.n * Fk * sizeof(float), sb = (size_t)t.n * sizeof(float);
         // The feature packer: caller buffers that came from ctr_alloc_pinned are DMA'd in place;
         // pageable ones (a Java heap array, a numpy array) are packed into this slot's pinned slab.
         const int64_t* src_ids = t.ids;
@@ -694,8 +709,24 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
         if (!is_pinned(e, t.wts, wb)) { memcpy(s.h_wts, t.wts, wb); src_wts = s.h_wts; }
         const bool out_pinned = is_pinned(e, t.scores, sb);
         float* dst_scores = out_pinned ? t.scores : s.h_scores;
-        CUDA_TRY(cudaMemcpyAsync(s.d_ids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
-        CUDA_TRY(cudaMemcpyAsync(s.d_wts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
+        if (t.n_ctx == 0) {
+            CUDA_TRY(cudaMemcpyAsync(s.d_ids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(s.d_wts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
+        } else {
+            // shared context: ship the per-candidate fields once and the context list once, rebuild the
+            // reference layout [n, F] on the device (HBM bandwidth is cheap, the host link is not)
+            CUDA_TRY(cudaMemcpyAsync(s.d_cids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(s.d_cwts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
+            int64_t* d_ctx_ids = s.d_cids + (size_t)s.cap * m.F;
+            float* d_ctx_wts = s.d_cwts + (size_t)s.cap * m.F;
+            CUDA_TRY(cudaMemcpyAsync(d_ctx_ids, t.ctx_ids, (size_t)t.n_ctx * sizeof(int64_t), cudaMemcpyHostToDevice, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(d_ctx_wts, t.ctx_wts, (size_t)t.n_ctx * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+            const int64_t total = t.n * m.F;
+            expand_context_kernel<<<(int)std::min<int64_t>((total + 255) / 256, dc.model.num_sms * 16), 256, 0, s.stream>>>(
+                d_ctx_ids, d_ctx_wts, t.n_ctx, s.d_cids, s.d_cwts, t.n, m.F, s.d_ids, s.d_wts);
+            CUDA_TRY(cudaGetLastError());
+            e->launches.fetch_add(1, std::memory_order_relaxed);
+        }
         int32_t rc = score_on_slot(e, dc, s, s.d_ids, s.d_wts, t.n, s.d_scores);
         if (rc != CTR_OK) return rc;
         CUDA_TRY(cudaMemcpyAsync(dst_scores, s.d_scores, sb, cudaMemcpyDeviceToHost, s.stream));
@@ -751,6 +782,11 @@ void free_device_state(ctr_engine* e) {
         dc.worker_slots.clear();
         dc.dev_slots.clear();
         if (dc.model.dev >= 0) free_model(dc.model);
+        if (dc.sort_cap) {
+            cudaFree(dc.srt_scores); cudaFree(dc.srt_sorted); cudaFree(dc.srt_counts);
+            for (int i = 0; i < 2; ++i) { cudaFree(dc.srt_keys[i]); cudaFree(dc.srt_idx[i]); }
+            dc.sort_cap = 0;
+        }
     }
 }
 
@@ -890,17 +926,20 @@ int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out) {
     return CTR_OK;
 }
 
-int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out,
-                          ctr_callback cb, void* user, ctr_ticket* ticket) {
-    if (!e || !ticket) return fail(CTR_ERR_INVALID, "ctr_predict_async: null argument");
-    if (!e->loaded || e->shutting_down) return fail(CTR_ERR_STATE, "ctr_predict_async: weights not loaded or engine shutting down");
-    if (n_cand < 0 || (n_cand > 0 && (!ids || !wts || !scores_out))) return fail(CTR_ERR_INVALID, "ctr_predict_async: null buffer or negative count");
+static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx_ids, const float* ctx_wts, int32_t n_ctx,
+                              const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out, ctr_callback cb, void* user,
+                              ctr_ticket* ticket) {
+    if (!e || !ticket) return fail(CTR_ERR_INVALID, std::string(who) + ": null argument");
+    if (!e->loaded || e->shutting_down) return fail(CTR_ERR_STATE, std::string(who) + ": weights not loaded or engine shutting down");
+    if (n_cand < 0 || (n_cand > 0 && (!ids || !wts || !scores_out))) return fail(CTR_ERR_INVALID, std::string(who) + ": null buffer or negative count");
+    if (n_ctx < 0 || n_ctx >= e->m.F || (n_ctx > 0 && (!ctx_ids || !ctx_wts)))
+        return fail(CTR_ERR_INVALID, std::string(who) + ": the shared context must cover 0 .. F-1 leading fields");
     const int P = e->cfg.n_devices;
     int64_t b[CTR_MAX_DEVICES], en[CTR_MAX_DEVICES];
     split_bounds(n_cand, P, b, en);
     for (int i = 0; i < P; ++i)
         if (en[i] - b[i] > e->cfg.max_candidates)
-            return fail(CTR_ERR_CAPACITY, "ctr_predict_async: a shard exceeds max_candidates of this engine");
+            return fail(CTR_ERR_CAPACITY, std::string(who) + ": a shard exceeds max_candidates of this engine");
     auto req = std::make_shared<Request>();
     req->cb = cb; req->user = user;
     req->ticket = e->next_ticket.fetch_add(1);
@@ -917,11 +956,12 @@ int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, i
         return CTR_OK;
     }
     req->pending = shards;
-    const int F = e->m.F;
+    const int Fk = e->m.F - n_ctx;
     for (int i = 0; i < P; ++i) {
         if (en[i] == b[i]) continue;
         Task t;
-        t.req = req; t.ids = ids + b[i] * F; t.wts = wts + b[i] * F; t.n = en[i] - b[i]; t.scores = scores_out + b[i];
+        t.req = req; t.ids = ids + b[i] * Fk; t.wts = wts + b[i] * Fk; t.n = en[i] - b[i]; t.scores = scores_out + b[i];
+        t.ctx_ids = ctx_ids; t.ctx_wts = ctx_wts; t.n_ctx = n_ctx;
         DeviceCtx& dc = *e->devs[i];
         {
             std::lock_guard<std::mutex> lk(dc.q_mu);
@@ -930,6 +970,17 @@ int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, i
         dc.q_cv.notify_one();
     }
     return CTR_OK;
+}
+
+int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out,
+                          ctr_callback cb, void* user, ctr_ticket* ticket) {
+    return submit_request(e, "ctr_predict_async", nullptr, nullptr, 0, ids, wts, n_cand, scores_out, cb, user, ticket);
+}
+
+int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const float* ctx_wts, int32_t n_ctx_fields,
+                                 const int64_t* cand_ids, const float* cand_wts, int64_t n_cand, float* scores_out,
+                                 ctr_callback cb, void* user, ctr_ticket* ticket) {
+    return submit_request(e, "ctr_predict_shared_async", ctx_ids, ctx_wts, n_ctx_fields, cand_ids, cand_wts, n_cand, scores_out, cb, user, ticket);
 }
 
 int32_t ctr_wait(ctr_engine* e, ctr_ticket ticket, int32_t timeout_ms) {
@@ -961,6 +1012,102 @@ int32_t ctr_predict(ctr_engine* e, const int64_t* ids, const float* wts, int64_t
     int32_t rc = ctr_predict_async(e, ids, wts, n_cand, scores_out, nullptr, nullptr, &t);
     if (rc != CTR_OK) return rc;
     return ctr_wait(e, t, -1);
+}
+
+// DC:195 on the device.  The merged scores (host) go to device 0 of the engine, are sorted there with
+// their candidate indices, and come back; 8 bytes per candidate each way next to 468 going in.
+int32_t ctr_predict_sorted(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* sorted_scores_out,
+                           int32_t* order_out) {
+    if (!e || (n_cand > 0 && !sorted_scores_out)) return fail(CTR_ERR_INVALID, "ctr_predict_sorted: null argument");
+    if (n_cand > INT32_MAX / 2) return fail(CTR_ERR_CAPACITY, "ctr_predict_sorted: too many candidates");
+    int32_t rc = ctr_predict(e, ids, wts, n_cand, sorted_scores_out);          // unsorted, ordered merge (DC:161-164)
+    if (rc != CTR_OK || n_cand == 0) return rc;
+    DeviceCtx& dc = *e->devs[0];
+    std::lock_guard<std::mutex> lk(dc.sort_mu);
+    CUDA_TRY(cudaSetDevice(dc.model.dev));
+    const int n = (int)n_cand;
+    const int n_blocks = (n + kSortTile - 1) / kSortTile;
+    if (dc.sort_cap < n_cand) {
+        if (dc.sort_cap) {
+            cudaFree(dc.srt_scores); cudaFree(dc.srt_sorted); cudaFree(dc.srt_counts);
+            for (int i = 0; i < 2; ++i) { cudaFree(dc.srt_keys[i]); cudaFree(dc.srt_idx[i]); }
+            dc.sort_cap = 0;
+        }
+        const int64_t cap = std::max<int64_t>(n_cand, e->cfg.max_candidates * (int64_t)e->cfg.n_devices);
+        CUDA_TRY(cudaMalloc(&dc.srt_scores, cap * sizeof(float)));
+        CUDA_TRY(cudaMalloc(&dc.srt_sorted, cap * sizeof(float)));
+        for (int i = 0; i < 2; ++i) {
+            CUDA_TRY(cudaMalloc(&dc.srt_keys[i], cap * sizeof(uint32_t)));
+            CUDA_TRY(cudaMalloc(&dc.srt_idx[i], cap * sizeof(int32_t)));
+        }
+        CUDA_TRY(cudaMalloc(&dc.srt_counts, (size_t)256 * ((cap + kSortTile - 1) / kSortTile) * sizeof(uint32_t)));
+        dc.sort_cap = cap;
+    }
+    cudaStream_t st = dc.main_stream;
+    CUDA_TRY(cudaMemcpyAsync(dc.srt_scores, sorted_scores_out, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, st));
+    const int g1 = std::max(1, std::min((n + 255) / 256, dc.model.num_sms * 8));
+    sort_make_keys_kernel<<<g1, 256, 0, st>>>(dc.srt_scores, n, dc.srt_keys[0], dc.srt_idx[0]);
+    int cur = 0;
+    for (int pass = 0; pass < 4; ++pass) {
+        sort_hist_kernel<<<n_blocks, kSortThreads, 0, st>>>(dc.srt_keys[cur], n, pass * 8, dc.srt_counts);
+        sort_scan_kernel<<<1, 1024, 0, st>>>(dc.srt_counts, 256 * n_blocks);
+        sort_scatter_kernel<<<n_blocks, kSortThreads, 0, st>>>(dc.srt_keys[cur], dc.srt_idx[cur], n, pass * 8, dc.srt_counts,
+                                                              dc.srt_keys[cur ^ 1], dc.srt_idx[cur ^ 1]);
+        cur ^= 1;
+    }
+    sort_gather_scores_kernel<<<g1, 256, 0, st>>>(dc.srt_scores, dc.srt_idx[cur], n, dc.srt_sorted);
+    CUDA_TRY(cudaGetLastError());
+    e->launches.fetch_add(14, std::memory_order_relaxed);
+    CUDA_TRY(cudaMemcpyAsync(sorted_scores_out, dc.srt_sorted, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (order_out) CUDA_TRY(cudaMemcpyAsync(order_out, dc.srt_idx[cur], (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return CTR_OK;
+}
+
+// The RPC itself (DC:112): serialised PredictRequest in, serialised PredictResponse out.
+int32_t ctr_predict_wire(ctr_engine* e, const void* request, int64_t request_len, void* response, int64_t response_cap,
+                         int64_t* response_len) {
+    if (!e || !request || request_len < 0 || !response_len) return fail(CTR_ERR_INVALID, "ctr_predict_wire: null argument");
+    if (!e->loaded) return fail(CTR_ERR_STATE, "ctr_predict_wire: weights not loaded");
+    std::vector<int64_t> ids;
+    std::vector<float> wts;
+    std::string model, sig, why;
+    if (!ctr_wire::parse_predict_request(static_cast<const uint8_t*>(request), (size_t)request_len, e->m.F, &ids, &wts, &model, &sig, &why))
+        return fail(CTR_ERR_INVALID, "ctr_predict_wire: " + why);
+    const int64_t n = (int64_t)ids.size() / e->m.F;
+    std::vector<float> scores((size_t)n);
+    int32_t rc = ctr_predict(e, ids.data(), wts.data(), n, scores.data());
+    if (rc != CTR_OK) return rc;
+    const std::string out = ctr_wire::build_predict_response(scores.data(), n, model, sig);
+    *response_len = (int64_t)out.size();
+    if (!response || response_cap < (int64_t)out.size()) return fail(CTR_ERR_CAPACITY, "ctr_predict_wire: response buffer too small (needed size is in *response_len)");
+    memcpy(response, out.data(), out.size());
+    return CTR_OK;
+}
+
+// Wire helpers without an engine (pure host code): what ctr_predict_wire does on either side of the scoring.
+int32_t ctr_wire_parse_request(const void* request, int64_t request_len, int32_t field_num, int64_t* ids_out, float* wts_out,
+                               int64_t cap_elems, int64_t* n_cand) {
+    if (!request || request_len < 0 || field_num < 1 || !n_cand) return fail(CTR_ERR_INVALID, "ctr_wire_parse_request: bad argument");
+    std::vector<int64_t> ids;
+    std::vector<float> wts;
+    std::string model, sig, why;
+    if (!ctr_wire::parse_predict_request(static_cast<const uint8_t*>(request), (size_t)request_len, field_num, &ids, &wts, &model, &sig, &why))
+        return fail(CTR_ERR_INVALID, "ctr_wire_parse_request: " + why);
+    *n_cand = (int64_t)ids.size() / field_num;
+    if ((int64_t)ids.size() > cap_elems || !ids_out || !wts_out) return fail(CTR_ERR_CAPACITY, "ctr_wire_parse_request: output buffers too small");
+    memcpy(ids_out, ids.data(), ids.size() * sizeof(int64_t));
+    memcpy(wts_out, wts.data(), wts.size() * sizeof(float));
+    return CTR_OK;
+}
+
+int32_t ctr_wire_build_response(const float* scores, int64_t n_cand, void* response, int64_t response_cap, int64_t* response_len) {
+    if ((n_cand > 0 && !scores) || n_cand < 0 || !response_len) return fail(CTR_ERR_INVALID, "ctr_wire_build_response: bad argument");
+    const std::string out = ctr_wire::build_predict_response(scores, n_cand, "DCN", "serving_default");
+    *response_len = (int64_t)out.size();
+    if (!response || response_cap < (int64_t)out.size()) return fail(CTR_ERR_CAPACITY, "ctr_wire_build_response: response buffer too small");
+    memcpy(response, out.data(), out.size());
+    return CTR_OK;
 }
 
 int32_t ctr_alloc_pinned(ctr_engine* e, int64_t bytes, void** out) {

@@ -76,8 +76,11 @@ __device__ __forceinline__ float ldg_nc_f1(const void* p) {
 
 // kTableDtype: 0 fp32 rows, 1 f16 rows.  kHashed: row = mix64(id) & (V-1).  kEmb: write X.
 // kLin: first-order sum.  kFM: DeepFM second-order term.  kSharded: rows striped over peers.
+#ifndef CTR_GATHER_MIN_CTAS
+#define CTR_GATHER_MIN_CTAS 4
+#endif
 template <int kTableDtype, bool kHashed, bool kEmb, bool kLin, bool kFM, bool kSharded>
-__global__ void __launch_bounds__(kGatherThreads)
+__global__ void __launch_bounds__(kGatherThreads, CTR_GATHER_MIN_CTAS)
 gather_pool_kernel(const GatherParams p) {
     extern __shared__ __align__(128) uint8_t gsm[];
     const int F = p.F;
@@ -279,6 +282,22 @@ __global__ void pack_table_kernel(uint8_t* table, uint64_t dst_row0, const float
             *reinterpret_cast<uint2*>(rp + q * 8) = o;
         }
         if (q == 0) *reinterpret_cast<float*>(rp + RowLayout<kTableDtype>::w1_off) = w1[r];
+    }
+}
+
+// Shared-context requests: the reference replicates every user / context
+// field for every candidate (DCNClient.java:61-63, :70-72).  Here the context list crosses the host
+// link once; this kernel rebuilds the reference layout [n, F] in HBM: field f < n_ctx of every
+// candidate comes from the shared list, the rest from the candidate's own compact list.
+__global__ void expand_context_kernel(const int64_t* ctx_ids, const float* ctx_wts, int n_ctx, const int64_t* cand_ids,
+                                      const float* cand_wts, int64_t n, int F, int64_t* ids_out, float* wts_out) {
+    const int Fk = F - n_ctx;
+    const int64_t total = n * F;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t b = i / F;
+        const int f = (int)(i - b * F);
+        ids_out[i] = f < n_ctx ? ctx_ids[f] : cand_ids[b * Fk + (f - n_ctx)];
+        wts_out[i] = f < n_ctx ? ctx_wts[f] : cand_wts[b * Fk + (f - n_ctx)];
     }
 }
 

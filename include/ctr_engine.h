@@ -109,12 +109,49 @@ int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out);
 int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand,
                           float* scores_out, ctr_callback cb, void* user, ctr_ticket* ticket);
 
+/* Shared-context request (additive).  The reference ships every user /
+ * context field again for every candidate (DC:61-63, DC:70-72).  Here the first n_ctx_fields of
+ * the F fields are given once (ctx_ids / ctx_wts, n_ctx_fields entries) and cand_ids / cand_wts
+ * hold only the remaining F - n_ctx_fields fields per candidate, row-major
+ * [n_cand, F - n_ctx_fields].  Scores are exactly those of ctr_predict_async on the expanded
+ * [n_cand, F] lists; the host link carries (F - n_ctx_fields) * 12 bytes per candidate instead
+ * of F * 12.  The context lists are read when the shards are staged: keep them valid until the
+ * ticket completes. */
+int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const float* ctx_wts, int32_t n_ctx_fields,
+                                 const int64_t* cand_ids, const float* cand_wts, int64_t n_cand, float* scores_out,
+                                 ctr_callback cb, void* user, ctr_ticket* ticket);
+
 /* Blocks like CompletableFuture.join (DC:158-159).  timeout_ms < 0 waits for ever.  On
  * CTR_OK or a failure status the ticket is released; on CTR_ERR_TIMEOUT it stays valid. */
 int32_t ctr_wait(ctr_engine* e, ctr_ticket ticket, int32_t timeout_ms);
 
 /* Synchronous convenience: ctr_predict_async + ctr_wait. */
 int32_t ctr_predict(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out);
+
+/* The same request followed by the reference's ascending sort of the merged scores
+ * (Collections.sort(fullCtrList), DC:195; Float.compareTo order: -0.0 < +0.0, NaN last), done on
+ * the device.  order_out (may be NULL) receives the candidate index of every sorted score --
+ * the identity the reference's sort throws away; ties keep candidate order (stable). */
+int32_t ctr_predict_sorted(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand,
+                           float* sorted_scores_out, int32_t* order_out);
+
+/* The RPC itself (stub.predict(request.build()), DC:111-112): a serialised
+ * tensorflow.serving.PredictRequest exactly as DCNClient builds it (inputs "feat_ids" DT_INT64 and
+ * "feat_wts" DT_FLOAT of shape [n, FIELD_NUM], as int64_val / float_val or tensor_content) in, a
+ * serialised PredictResponse with outputs["prediction_node"] (DT_FLOAT [n, 1], float_val; DC:35,
+ * DC:162) out.  A malformed or inconsistent request fails with CTR_ERR_INVALID, as the server
+ * would answer INVALID_ARGUMENT.  If response_cap is too small the call fails with
+ * CTR_ERR_CAPACITY and *response_len holds the size needed. */
+int32_t ctr_predict_wire(ctr_engine* e, const void* request, int64_t request_len, void* response,
+                         int64_t response_cap, int64_t* response_len);
+
+/* The two halves of ctr_predict_wire as pure host functions (no engine, no GPU): parse a
+ * PredictRequest into flat ids / weights (cap_elems = capacity of each output in elements), and
+ * serialise scores as the PredictResponse the reference client reads. */
+int32_t ctr_wire_parse_request(const void* request, int64_t request_len, int32_t field_num, int64_t* ids_out,
+                               float* wts_out, int64_t cap_elems, int64_t* n_cand);
+int32_t ctr_wire_build_response(const float* scores, int64_t n_cand, void* response, int64_t response_cap,
+                                int64_t* response_len);
 
 /* ---- pinned host memory for the zero-copy packer (north star (a)) ---- */
 int32_t ctr_alloc_pinned(ctr_engine* e, int64_t bytes, void** out);

@@ -171,3 +171,41 @@ def test_one_process_per_gpu_split_and_ordered_merge():
     assert all(p.exitcode == 0 for p in procs)
     results = [q.get(timeout=5) for _ in range(3)]
     assert sorted(r[0] for r in results) == [0, 2, 1001] and all(r[1] for r in results)
+
+
+# ---------------------------------------------------------------- wire-compat front door (host half)
+def test_wire_front_door_matches_oracle_codec(binding):
+    """The product's hand-written PredictRequest parser / PredictResponse writer against the oracle's
+    independent codec (both restate tensor.proto:48,64 and predict.proto:12-40)."""
+    from oracle import clib, model as om
+    ids, wts = om.criteo_inputs(37, n_sparse=30, rows_per_field=1 << 20)        # F = 43, the reference's FIELD_NUM
+    ids[3, 5] = -7                                                             # 10-byte varint
+    req = clib.encode_predict_request(ids, wts)                                # int64_val / float_val, as DCNClient.java:101,107
+    i2, w2 = binding.wire_parse_request(req, 43)
+    assert np.array_equal(i2, ids) and np.array_equal(w2, wts)
+    scores = np.linspace(0, 1, 37, dtype=np.float32)
+    resp = binding.wire_build_response(scores)
+    assert np.array_equal(clib.decode_predict_response(resp, 37), scores)
+    assert b"prediction_node" in resp and b"DCN" in resp
+    # tensor_content variant (raw little-endian bytes), built by hand from the field numbers
+    def varint(v):
+        out = b""
+        while v >= 0x80:
+            out += bytes([v & 0x7F | 0x80]); v >>= 7
+        return out + bytes([v])
+    def ld(field, payload):
+        return varint(field << 3 | 2) + varint(len(payload)) + payload
+    shape = b"".join(ld(2, varint(1 << 3) + varint(d)) for d in (37, 43))
+    t_ids = varint(1 << 3) + varint(9) + ld(2, shape) + ld(4, ids.astype("<i8").tobytes())
+    t_wts = varint(1 << 3) + varint(1) + ld(2, shape) + ld(4, wts.astype("<f4").tobytes())
+    req2 = ld(2, ld(1, b"feat_wts") + ld(2, t_wts)) + ld(2, ld(1, b"feat_ids") + ld(2, t_ids)) + ld(1, ld(1, b"DCN"))
+    i3, w3 = binding.wire_parse_request(req2, 43)
+    assert np.array_equal(i3, ids) and np.array_equal(w3, wts)
+    # INVALID_ARGUMENT cases: wrong FIELD_NUM, value count vs shape, missing input, truncated message
+    for bad, f in ((req, 39), (req[:len(req) - 9], 43), (ld(2, ld(1, b"feat_ids") + ld(2, t_ids)), 43), (req2[:50], 43)):
+        with pytest.raises(binding.CtrError) as ei:
+            binding.wire_parse_request(bad, f)
+        assert ei.value.code == -1
+    short = varint(1 << 3) + varint(9) + ld(2, shape) + ld(10, b"".join(varint(1) for _ in range(10)))   # 10 values, shape 37x43
+    with pytest.raises(binding.CtrError):
+        binding.wire_parse_request(ld(2, ld(1, b"feat_ids") + ld(2, short)) + ld(2, ld(1, b"feat_wts") + ld(2, t_wts)), 43)

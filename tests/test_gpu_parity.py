@@ -260,3 +260,69 @@ def test_device_resident_matches_host_path(binding, om, weight_file):
     assert np.array_equal(a, host)
     assert np.array_equal(d_out2.cpu().numpy(), host)
     assert e is not None
+
+
+# ---------------------------------------------------------------- A6: the sort of processARequest, on the device
+@pytest.mark.parametrize("n", [1, 257, 10000, 70000])
+def test_predict_sorted_matches_java_order(binding, om, weight_file, n):
+    from oracle import dcn_client as odc
+    w = make_case(om.DEEPFM, hidden=(256, 128))
+    e = _engine(binding, weight_file(w), max_candidates=70000)
+    ids, wts = om.criteo_inputs(n, seed=n, rows_per_field=1 << 10)
+    ids[n // 2:] = ids[:n - n // 2]                       # duplicates -> ties, to exercise stability
+    wts[n // 2:] = wts[:n - n // 2]
+    plain = e.predict(ids, wts).copy()
+    srt, order = e.predict_sorted(ids, wts)
+    e.close()
+    ref_order = np.argsort(odc.java_float_sort_key(plain), kind="stable")
+    assert np.array_equal(order, ref_order.astype(np.int32)), "candidate indices of the sorted scores (stable)"
+    assert np.array_equal(srt, plain[ref_order]) and np.array_equal(srt, odc.java_float_sort(plain))
+
+
+def test_predict_sorted_reference_inputs_and_special_values(binding, om, weight_file):
+    """With the reference's demo inputs every score is equal: the sort is the identity permutation."""
+    w = make_case(om.LR, F=43, procedural=False)
+    e = _engine(binding, weight_file(w), max_candidates=2048)
+    ids = np.tile(np.arange(1, 44, dtype=np.int64), (1500, 1))
+    srt, order = e.predict_sorted(ids, np.ones((1500, 43), np.float32))
+    assert np.all(srt == srt[0]) and np.array_equal(order, np.arange(1500, dtype=np.int32))
+    # weights chosen to produce +-0.0-like extremes: sigmoid saturates to exactly 0.0 and 1.0
+    wts = np.zeros((4, 43), np.float32)
+    wts[0, :] = 1e30; wts[1, :] = -1e30; wts[2, :] = 0.0; wts[3, :] = 1.0
+    srt, order = e.predict_sorted(np.tile(np.arange(1, 44, dtype=np.int64), (4, 1)), wts)
+    e.close()
+    assert np.all(np.diff(srt[~np.isnan(srt)]) >= 0) and sorted(order.tolist()) == [0, 1, 2, 3]
+
+
+# ---------------------------------------------------------------- f2: the RPC itself, wire format in and out
+def test_predict_wire_is_a_drop_in_for_the_rpc(binding, om, weight_file):
+    from oracle import clib
+    w = make_case(om.WIDE_DEEP, hidden=(256, 128))
+    e = _engine(binding, weight_file(w), max_candidates=4096)
+    ids, wts = om.criteo_inputs(1000, rows_per_field=1 << 10)
+    want = e.predict(ids, wts).copy()
+    resp = e.predict_wire(clib.encode_predict_request(ids, wts))           # built like DCNClient.java:97-109
+    got = clib.decode_predict_response(resp, 1000)                         # read like DCNClient.java:162
+    assert np.array_equal(got, want)
+    with pytest.raises(binding.CtrError) as ei:                             # shape [n, 38] for a 39-field model
+        e.predict_wire(clib.encode_predict_request(ids[:, :38].copy(), wts[:, :38].copy()))
+    assert ei.value.code == -1
+    e.close()
+
+
+# ---------------------------------------------------------------- f1: shared-context requests
+@pytest.mark.parametrize("n_ctx", [1, 13, 26, 38])
+def test_shared_context_equals_replicated_fields(binding, om, weight_file, n_ctx):
+    """The context fields given once must score exactly like the reference layout that repeats them
+    for every candidate (DCNClient.java:61-63)."""
+    w = make_case(om.DEEPFM, hidden=(256, 128))
+    e = _engine(binding, weight_file(w), max_candidates=4096)
+    ids, wts = om.criteo_inputs(2001, seed=n_ctx, rows_per_field=1 << 10)
+    ids[:, :n_ctx] = ids[0, :n_ctx]                         # a real request: same user / context for all candidates
+    wts[:, :n_ctx] = wts[0, :n_ctx]
+    want = e.predict(ids, wts).copy()
+    t, out = e.predict_shared_async(ids[0, :n_ctx], wts[0, :n_ctx], np.ascontiguousarray(ids[:, n_ctx:]), np.ascontiguousarray(wts[:, n_ctx:]))
+    got = e.wait(t)
+    e.close()
+    assert np.array_equal(got, want)
+    assert np.abs(want - om.forward(w, ids, wts, "fp64")).max() <= TOL_F16
