@@ -268,18 +268,23 @@ def main():
     assert np.isfinite(d_out[:1000].cpu().numpy()).all()
 
     peaks = load_peaks()
+    try:    # DRAM bytes per candidate measured by ncu (--set full) for each kernel, committed under profiles/
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except Exception:
+        traffic = {}
+    per_cand = lambda k: (traffic.get(k) or {}).get("dram_bytes_per_candidate")
     rl = []
     if stage_ms["gather"] > 0:
         a = GATHER_BYTES_PER_CAND * chunk_rows / (stage_ms["gather"] * 1e-3) / 1e9
         rl.append({"kernel": "gather_pool_kernel", "bound": "hbm", "achieved": a, "peak": peaks["hbm"], "unit": "GB/s",
-                   "frac": a / peaks["hbm"], "traffic": None, "ms": stage_ms["gather"],
+                   "frac": a / peaks["hbm"], "traffic": (per_cand("gather_pool_kernel") or 0) * chunk_rows or None, "ms": stage_ms["gather"],
                    "algorithmic_bytes_per_candidate": GATHER_BYTES_PER_CAND})
     if stage_ms["tower"] > 0:
         flop = sum(FLOP_PER_CAND_LAYER)
         a = flop * chunk_rows / (stage_ms["tower"] * 1e-3) / 1e12
         rl.append({"kernel": "tower_chain_kernel (624->1024->512->256->1 in one launch)", "bound": "tensor", "achieved": a,
-                   "peak": peaks["tc_sustained"], "unit": "TFLOP/s", "frac": a / peaks["tc_sustained"], "traffic": None,
-                   "ms": stage_ms["tower"], "algorithmic_flop_per_candidate": flop,
+                   "peak": peaks["tc_sustained"], "unit": "TFLOP/s", "frac": a / peaks["tc_sustained"],
+                   "traffic": (per_cand("tower_chain_kernel") or 0) * chunk_rows or None, "ms": stage_ms["tower"], "algorithmic_flop_per_candidate": flop,
                    "frac_of_burst_peak": a / peaks["tc_burst"]})
     dominant = max(rl, key=lambda r: r["ms"]) if rl else None
     if dominant is not None:
@@ -324,7 +329,44 @@ def main():
         ts = np.sort(np.array(ts[10:]))
         lat = {"p50_ms": float(np.percentile(ts, 50)), "p99_ms": float(np.percentile(ts, 99)), "n": int(ts.size),
                "what": "one %d-candidate request through ctr_predict (H2D + kernels + D2H), sequential" % C}
-        for b in (pin_i, pin_w, pin_o):
+        # the same window including the reference's sort (DC:195), done on the device
+        ts2 = []
+        for _ in range(max(20, args.latency_requests // 4)):
+            t0 = time.perf_counter()
+            eng.predict_sorted(pin_i.array[:C], pin_w.array[:C])
+            ts2.append((time.perf_counter() - t0) * 1e3)
+        ts2 = np.sort(np.array(ts2[5:]))
+        lat["with_sort_p50_ms"] = float(np.percentile(ts2, 50))
+        lat["with_sort_p99_ms"] = float(np.percentile(ts2, 99))
+        # additive API: 26 user/context fields given once per request, 13 per-candidate fields shipped
+        n_ctx = 26
+        fk = F - n_ctx
+        pin_ci, pin_cw = eng.pinned((n, fk), np.int64), eng.pinned((n, fk), np.float32)
+        pin_ci.array[:] = h_ids_t[:, n_ctx:]
+        pin_cw.array[:] = h_wts_t[:, n_ctx:]
+        ctx_i = [np.ascontiguousarray(h_ids_t[r * C, :n_ctx]) for r in range(R)]
+        ctx_w = [np.ascontiguousarray(h_wts_t[r * C, :n_ctx]) for r in range(R)]
+
+        def shared_step():
+            tickets = []
+            for r in range(R):
+                t, _ = eng.predict_shared_async(ctx_i[r], ctx_w[r], pin_ci.array[r * C:(r + 1) * C], pin_cw.array[r * C:(r + 1) * C],
+                                                out=pin_o.array[r * C:(r + 1) * C])
+                tickets.append(t)
+            for t in tickets:
+                eng.wait(t)
+        for _ in range(args.warmup):
+            shared_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            shared_step()
+        torch.cuda.synchronize()
+        t_sh = max_over_ranks(time.perf_counter() - t0)
+        e2e["shared_context"] = {"value": world * n * args.steps / t_sh, "unit": "candidates/s", "h2d_bytes_per_step": n * fk * 12 + R * n_ctx * 12,
+                                 "d2h_bytes_per_step": n * 4, "what": "ctr_predict_shared_async: 26 of 39 fields (13 dense + 13 sparse) given once per request, "
+                                 "13 per-candidate fields shipped; additive API beside the drop-in one"}
+        for b in (pin_i, pin_w, pin_o, pin_ci, pin_cw):
             b.free()
 
     # ---------------- CPU baseline (rank 0, N=1 only) ----------------
