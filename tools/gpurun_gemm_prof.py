@@ -1,6 +1,6 @@
 import os, sys, tempfile
 import numpy as np
-sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import dtfs_b200
 from dtfs_b200 import binding, weights as W
 os.environ["CTR_GEMM_PROF"] = "1"
