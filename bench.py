@@ -50,19 +50,42 @@ def load_peaks():
     return dict(hbm=6650.0, tc_burst=1590.0, tc_sustained=1400.0, src="fallback")
 
 
-def write_model(path: str, rows_per_field: int, seed: int = 1234):
-    """Random-init Wide&Deep of the config-2 architecture; procedural table (no 7 GB file)."""
+# the other model families of BASELINE.json (configs 3 and 4): secondary runs, `--model`
+MODELS = {"wide_deep": dict(kind=1, hidden=(1024, 512, 256), n_cross=0),       # SURVEY.md section 8(a-M) shapes
+          "deepfm": dict(kind=2, hidden=(512, 512, 512), n_cross=0),
+          "dcn_v2": dict(kind=3, hidden=(1024, 512, 256), n_cross=3)}
+
+
+def model_flop_per_candidate(model: str) -> int:
+    m = MODELS[model]
+    d, fl, fan_in = F * EMB, 0, F * EMB
+    for h in m["hidden"]:
+        fl += 2 * fan_in * h
+        fan_in = h
+    fl += m["n_cross"] * 2 * d * d
+    return fl + 2 * (m["hidden"][-1] + (d if m["kind"] == 3 else 0))
+
+
+def write_model(path: str, rows_per_field: int, seed: int = 1234, model: str = "wide_deep", table_dtype: int = 0, hashed: bool = False):
+    """Random-init model of the named architecture; procedural table (no multi-GB file)."""
     from dtfs_b200 import weights as W
+    m = MODELS[model]
     rng = np.random.Generator(np.random.PCG64(seed))
-    mlp, fan_in = [], F * EMB
-    for h in HIDDEN:
+    d = F * EMB
+    mlp, fan_in = [], d
+    for h in m["hidden"]:
         lim = np.sqrt(6.0 / (fan_in + h))
         mlp.append((rng.uniform(-lim, lim, (h, fan_in)).astype(np.float32), rng.uniform(-0.05, 0.05, h).astype(np.float32)))
         fan_in = h
-    w_out = rng.uniform(-1, 1, HIDDEN[-1]).astype(np.float32)
+    cross = [(rng.uniform(-0.03, 0.03, (d, d)).astype(np.float32), rng.uniform(-0.05, 0.05, d).astype(np.float32))
+             for _ in range(m["n_cross"])]
+    w_out = rng.uniform(-1, 1, m["hidden"][-1] + (d if m["kind"] == 3 else 0)).astype(np.float32)
     num_rows = N_DENSE + 1 + N_SPARSE * rows_per_field
-    W.write_weight_file(path, model_kind=W.MODEL_WIDE_DEEP, num_fields=F, num_rows=num_rows, b0=0.01,
-                        seed=seed, scale_e=0.25, scale_w1=0.5, mlp=mlp, w_out=w_out, b_out=-0.02)
+    if hashed:
+        num_rows = 1 << int(np.ceil(np.log2(num_rows)))
+    W.write_weight_file(path, model_kind=m["kind"], num_fields=F, num_rows=num_rows, b0=0.01, table_dtype=table_dtype,
+                        id_mode=W.ID_HASHED if hashed else W.ID_DIRECT, seed=seed, scale_e=0.25, scale_w1=0.5,
+                        mlp=mlp, cross=cross, w_out=w_out, b_out=-0.02)
     return num_rows
 
 
@@ -192,6 +215,9 @@ def main():
     ap.add_argument("--requests-per-step", type=int, default=64)
     ap.add_argument("--ref-requests-per-step", type=int, default=2)
     ap.add_argument("--rows-per-field", type=int, default=1 << 22)
+    ap.add_argument("--model", default="wide_deep", choices=sorted(MODELS), help="wide_deep is the headline (config 2); others are secondary runs")
+    ap.add_argument("--table-dtype", default="fp32", choices=["fp32", "f16"])
+    ap.add_argument("--hashed", action="store_true", help="row = mix64(id) & (V-1) (config 4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--latency-requests", type=int, default=300)
@@ -233,7 +259,9 @@ def main():
 
     tmp = tempfile.mkdtemp(prefix="ctr_bench_%d_" % rank)
     wpath = os.path.join(tmp, "wd.ctrw")
-    num_rows = write_model(wpath, args.rows_per_field)
+    num_rows = write_model(wpath, args.rows_per_field, model=args.model, table_dtype=1 if args.table_dtype == "f16" else 0, hashed=args.hashed)
+    if args.model != "wide_deep" or args.table_dtype != "fp32" or args.hashed:
+        args.no_cpu_baseline = True                      # the CPU baseline is for the headline configuration
     C, R = args.candidates, args.requests_per_step
     n = C * R
     eng = binding.Engine(device_ids=(local_rank,), max_candidates=32768, workers_per_device=4)
@@ -262,7 +290,7 @@ def main():
     launches = eng.launch_count() - launches0
     clk = clocks.result()
     value = world * n * args.steps / t_dev
-    stage_ms = {"gather": eng.stage_ms(0), "tower": eng.stage_ms(1), "chunk": eng.stage_ms(-1)}
+    stage_ms = {"gather": eng.stage_ms(0), "tower": eng.stage_ms(1) + max(eng.stage_ms(2), 0.0), "chunk": eng.stage_ms(-1)}   # DCN-v2: cross chain + MLP chain
     eng.set_timing(False)
     chunk_rows = min(n, int(info.chunk_rows))          # candidates per kernel launch (first chunk is a full one)
     assert np.isfinite(d_out[:1000].cpu().numpy()).all()
@@ -275,12 +303,13 @@ def main():
     per_cand = lambda k: (traffic.get(k) or {}).get("dram_bytes_per_candidate")
     rl = []
     if stage_ms["gather"] > 0:
-        a = GATHER_BYTES_PER_CAND * chunk_rows / (stage_ms["gather"] * 1e-3) / 1e9
+        gbytes = F * 12 + N_SPARSE * ((EMB * 2 if args.table_dtype == "f16" else EMB * 4) + 4)
+        a = gbytes * chunk_rows / (stage_ms["gather"] * 1e-3) / 1e9
         rl.append({"kernel": "gather_pool_kernel", "bound": "hbm", "achieved": a, "peak": peaks["hbm"], "unit": "GB/s",
-                   "frac": a / peaks["hbm"], "traffic": (per_cand("gather_pool_kernel") or 0) * chunk_rows or None, "ms": stage_ms["gather"],
-                   "algorithmic_bytes_per_candidate": GATHER_BYTES_PER_CAND})
+                   "frac": a / peaks["hbm"], "traffic": ((per_cand("gather_pool_kernel") or 0) * chunk_rows or None) if (args.table_dtype == "fp32" and args.model == "wide_deep") else None, "ms": stage_ms["gather"],
+                   "algorithmic_bytes_per_candidate": gbytes})
     if stage_ms["tower"] > 0:
-        flop = sum(FLOP_PER_CAND_LAYER)
+        flop = model_flop_per_candidate(args.model)
         a = flop * chunk_rows / (stage_ms["tower"] * 1e-3) / 1e12
         rl.append({"kernel": "tower_chain_kernel (624->1024->512->256->1 in one launch)", "bound": "tensor", "achieved": a,
                    "peak": peaks["tc_sustained"], "unit": "TFLOP/s", "frac": a / peaks["tc_sustained"],
@@ -386,8 +415,9 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
             "config": {"workload": "wide_deep criteo 13 dense + 26 sparse dim16, 10k-candidate requests (BASELINE config 2)",
-                       "tower": "624->1024->512->256->1", "candidates_per_request": C, "requests_per_step": R,
-                       "candidates_per_step_per_gpu": n, "table_rows": int(num_rows), "table_dtype": "fp32",
+                       "model": args.model, "tower": "624->" + "->".join(map(str, MODELS[args.model]["hidden"])) + "->1" + (" + %d cross layers 624x624" % MODELS[args.model]["n_cross"] if MODELS[args.model]["n_cross"] else ""),
+                       "id_mode": "hashed" if args.hashed else "direct", "candidates_per_request": C, "requests_per_step": R,
+                       "candidates_per_step_per_gpu": n, "table_rows": int(num_rows), "table_dtype": args.table_dtype,
                        "table_bytes_per_gpu": int(info.table_bytes_per_device), "id_distribution": "uniform",
                        "l2": "inputs larger than L2 (%.0f MB ids+weights per step; %.1f GB table, random rows)" % (n * F * 12 / 1e6, info.table_bytes_per_device / 1e9),
                        "parallelism": "candidate-sharded x%d, tables replicated, no collective" % world},
