@@ -201,14 +201,17 @@ class Engine:
             raise ValueError("ids / wts need n_cand * %d elements each" % self.num_fields)
         return ids, wts, ids.size // self.num_fields
 
-    def predict_async(self, ids, wts, out: Optional[np.ndarray] = None):
+    def predict_async(self, ids, wts, out: Optional[np.ndarray] = None, callback=None):
+        """callback(ticket, status) runs on an engine thread when the request completes (the Java shim
+        completes its CompletableFuture there)."""
         ids, wts, n = self._check_inputs(ids, wts)
         if out is None:
             out = np.empty(n, np.float32)
         t = C.c_int64()
+        cb = CALLBACK(lambda user, ticket, status: callback(ticket, status)) if callback else None
         _check(self.lib.ctr_predict_async(self.handle, ids.ctypes.data, wts.ctypes.data, n, out.ctypes.data,
-                                          None, None, C.byref(t)))
-        self._keep[t.value] = (ids, wts, out)
+                                          C.cast(cb, C.c_void_p) if cb else None, None, C.byref(t)))
+        self._keep[t.value] = (ids, wts, cb, out)
         return t.value, out
 
     def predict_shared_async(self, ctx_ids, ctx_wts, cand_ids, cand_wts, out: Optional[np.ndarray] = None):

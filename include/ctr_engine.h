@@ -160,8 +160,10 @@ int32_t ctr_free_pinned(ctr_engine* e, void* p);
 /* ---- device-resident scoring: sendRequest (DC:91-115) with tensors already in HBM ----
  * d_ids / d_wts / d_scores are device pointers on device_ids[device_index]; stream is a
  * cudaStream_t (NULL = the engine's own stream for that device, and the call then returns
- * after the work has finished).  Used by bench.py's device-resident figure and by callers
- * that produce features on the GPU. */
+ * after the work has finished, with out-of-range ids reported as CTR_ERR_INVALID; with a caller
+ * stream the call only enqueues and such ids score as weight 0).  Calls on one device are
+ * serialised while they enqueue; do not overlap calls that use different caller streams.  Used by
+ * bench.py's device-resident figure and by callers that produce features on the GPU. */
 int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids, const void* d_wts,
                          int64_t n_cand, void* d_scores, void* stream);
 

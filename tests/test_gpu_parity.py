@@ -326,3 +326,31 @@ def test_shared_context_equals_replicated_fields(binding, om, weight_file, n_ctx
     e.close()
     assert np.array_equal(got, want)
     assert np.abs(want - om.forward(w, ids, wts, "fp64")).max() <= TOL_F16
+
+
+def test_callback_and_timeout(binding, om, weight_file):
+    """Completion callback (what the Java shim hangs its CompletableFuture on) and ctr_wait's timeout."""
+    import threading
+    w = make_case(om.WIDE_DEEP, hidden=(1024, 512, 256))
+    e = _engine(binding, weight_file(w), max_candidates=16384, workers_per_device=1)
+    ids, wts = om.criteo_inputs(16000, rows_per_field=1 << 10)
+    done = threading.Event()
+    seen = {}
+
+    def cb(ticket, status):
+        seen["ticket"], seen["status"] = ticket, status
+        done.set()
+    tickets = [e.predict_async(ids, wts)[0] for _ in range(40)]            # keep the single worker busy for tens of ms
+    t_cb, out = e.predict_async(ids, wts, callback=cb)
+    with pytest.raises(binding.CtrError) as ei:                             # not ready within 0 ms behind 40 requests
+        e.wait(t_cb, timeout_ms=0)
+    assert ei.value.code == -5
+    assert done.wait(30) and seen == {"ticket": t_cb, "status": 0}
+    got = e.wait(t_cb)                                                      # the ticket survived the timeout
+    for t in tickets:
+        e.wait(t)
+    with pytest.raises(binding.CtrError) as ei:                             # released tickets are unknown
+        e.wait(t_cb)
+    assert ei.value.code == -4
+    assert np.array_equal(got, e.predict(ids, wts))
+    e.close()
