@@ -354,3 +354,30 @@ def test_callback_and_timeout(binding, om, weight_file):
     assert ei.value.code == -4
     assert np.array_equal(got, e.predict(ids, wts))
     e.close()
+
+
+# ---------------------------------------------------------------- odd shapes: padding paths
+@pytest.mark.parametrize("kind_name,F,hidden,n_cross", [
+    ("wide_deep", 48, (200,), 0),             # widest field count, one hidden layer padded 200 -> 256
+    ("wide_deep", 14, (72, 40), 0),           # 13 dense + 1 sparse, tiny layers padded to 128
+    ("deepfm", 39, (640, 384, 128, 64), 0),   # four hidden layers, BN = 128 tiles
+    ("dcn_v2", 20, (136, 8), 1),              # d = 320 (pad 384), single cross layer, last hidden layer of 8
+    ("dcn_v2", 43, (256, 256), 4),            # reference FIELD_NUM, four cross layers (d = 688, pad 768)
+])
+def test_odd_shapes(binding, om, weight_file, kind_name, F, hidden, n_cross):
+    kind = {"wide_deep": om.WIDE_DEEP, "deepfm": om.DEEPFM, "dcn_v2": om.DCN_V2}[kind_name]
+    rpf = 1 << 9
+    spec = om.ModelSpec(kind, F, 16, om.criteo_num_rows(13, F - 13, rpf), hidden=tuple(hidden), n_cross=n_cross,
+                        table_mode=om.TABLE_PROCEDURAL, scale_e=0.25)
+    w = om.make_weights(spec, calib_inputs=om.criteo_inputs(256, seed=99, n_sparse=F - 13, rows_per_field=rpf))
+    e = _engine(binding, weight_file(w), max_candidates=2048)
+    for n in (1, 300, 1025):
+        ids, wts = om.criteo_inputs(n, seed=n, n_sparse=F - 13, rows_per_field=rpf)
+        got = e.predict(ids, wts)
+        p64 = om.forward(w, ids, wts, "fp64")
+        pemu = om.forward(w, ids, wts, "f16")
+        # 2x the usual emulation tolerance: with four layers (and DeepFM's larger logits) more activations
+        # sit on a half-precision rounding boundary, where the accumulation order decides the rounding
+        assert np.abs(got - pemu).max() <= 2 * TOL_F16_EMU, "n=%d vs kernel-contract oracle: %g" % (n, np.abs(got - pemu).max())
+        assert np.abs(got - p64).max() <= TOL_F16, "n=%d vs fp64 master: %g" % (n, np.abs(got - p64).max())
+    e.close()
