@@ -470,7 +470,7 @@ int32_t build_chains(ctr_engine* e, DeviceModel& dm, Slot& s) {
             const bool last = l == c.n_layers - 1;
             const int out = is_cross ? 3 + (l & 1) : 1 + (l & 1);
             if (s.ld[a] < L.Kpad) return fail(CTR_ERR_INVALID, "internal: activation buffer narrower than the layer's K");
-            const int a_rows = a == 0 ? s.x_rows : s.scratch_rows;
+            const int a_rows = a == 0 ? s.x_rows : 2 * s.scratch_rows;     // two interleaved tiles per CTA pair
             if ((rc = make_map_f16(&c.maps.a[l], s.buf[a], (uint64_t)a_rows, (uint64_t)L.Kpad, (uint64_t)s.ld[a], kBM)) != CTR_OK) return rc;
             if ((rc = make_map_f16(&c.maps.w[l], L.W, (uint64_t)L.Npad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, c.BN / 2)) != CTR_OK) return rc;
             ChainLayer& cl = c.params.layer[l];
@@ -543,11 +543,11 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     };
     int32_t rc;
     if ((rc = alloc_buf(0, s.x_rows, dpad)) != CTR_OK) return rc;
-    if ((rc = alloc_buf(1, s.scratch_rows, maxn)) != CTR_OK) return rc;
-    if ((rc = alloc_buf(2, s.scratch_rows, maxn)) != CTR_OK) return rc;
+    if ((rc = alloc_buf(1, 2 * s.scratch_rows, maxn)) != CTR_OK) return rc;        // 2 tiles in flight per CTA pair
+    if ((rc = alloc_buf(2, 2 * s.scratch_rows, maxn)) != CTR_OK) return rc;
     if (m.kind == CTR_MODEL_DCN_V2) {
-        if ((rc = alloc_buf(3, s.scratch_rows, dpad)) != CTR_OK) return rc;
-        if ((rc = alloc_buf(4, s.scratch_rows, dpad)) != CTR_OK) return rc;
+        if ((rc = alloc_buf(3, 2 * s.scratch_rows, dpad)) != CTR_OK) return rc;
+        if ((rc = alloc_buf(4, 2 * s.scratch_rows, dpad)) != CTR_OK) return rc;
     }
     return build_chains(e, dm, s);
 }
@@ -1411,7 +1411,7 @@ extern "C" int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, 
     // A slot whose buffers are slices of the fixed array; nothing in it is allocated or freed.
     Slot s;
     s.dev = dm.dev; s.stream = st; s.owns_stream = false;
-    s.cap = kStaticMaxCandidates; s.x_rows = kStaticMaxCandidates; s.scratch_rows = kStaticMaxCandidates;
+    s.cap = kStaticMaxCandidates; s.x_rows = kStaticMaxCandidates; s.scratch_rows = kStaticMaxCandidates / 2;   // 2 CTA pairs x 2 tiles each
     unsigned char* p = base;
     s.buf[0] = reinterpret_cast<__half*>(p); p += kStaticXBytes;
     s.buf[1] = reinterpret_cast<__half*>(p); p += kStaticHBytes;

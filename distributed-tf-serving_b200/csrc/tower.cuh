@@ -16,7 +16,9 @@
 // and walks it through every layer of the chain; the intermediate activations of that tile go to
 // a small per-pair scratch that never leaves L2, the accumulators stay double-buffered across
 // layer boundaries, and the W tiles of the next layer are already in flight while the previous
-// layer's epilogue drains.
+// layer's epilogue drains.  A pair keeps TWO tiles in flight and alternates between them layer by
+// layer: a layer can only start when the previous layer's last epilogue has stored its rows, and
+// while one tile sits at that boundary the tensor cores work on the other one.
 //
 // Structure (CTAs paired into clusters of 2 = one TPC, persistent, 384 threads per CTA):
 //   warp 0     TMA producer: cp.async.bulk.tensor 2-D loads (128-byte swizzle) of this CTA's 128
@@ -195,8 +197,8 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     uint64_t* empty_bar = bars + kStages;          // [kStages] in each CTA: MMA -> that CTA's producer
     uint64_t* acc_full = bars + 2 * kStages;       // [2] in each CTA: MMA -> that CTA's epilogue
     uint64_t* acc_empty = bars + 2 * kStages + 2;  // [2] used in the leader: both CTAs' epilogues -> MMA
-    uint64_t* layer_done = bars + 2 * kStages + 4; // [1] in each CTA: epilogue (layer l stored) -> producer (layer l+1 A loads)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 5);
+    uint64_t* layer_done = bars + 2 * kStages + 4; // [2] in each CTA, one per interleaved tile: epilogue (layer l stored) -> producer (layer l+1 A loads)
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 6);
     __shared__ float dot_part[2 * kBM];            // high-column-half partial dots, double-buffered
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -212,7 +214,8 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 2); mbar_init(&empty_bar[s], 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 16); }
-        mbar_init(layer_done, 8);
+        mbar_init(&layer_done[0], 8);
+        mbar_init(&layer_done[1], 8);
         mbar_fence_init();
     }
     if (warp == 2) {
@@ -229,10 +232,13 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         if (lane == 0) {
             int s = 0; uint32_t ph = 0, ld_ph = 0;
             long long w_empty = 0, w_layer = 0;
-            for (int t = pair_id; t < tiles_m; t += n_pairs) {
+            for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
+                const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;             // two tiles in flight, layer by layer
                 for (int l = 0; l < nl; ++l) {
+                  for (int sub = 0; sub < n_sub; ++sub) {
                     const ChainLayer& L = p.layer[l];
-                    const int a_row = (L.a_global ? t : pair_id) * 2 * kBM + (int)rank * kBM;
+                    const int t = t0 + sub * n_pairs;
+                    const int a_row = (L.a_global ? t : pair_id * 2 + sub) * 2 * kBM + (int)rank * kBM;
                     const int tiles_n = L.N / BN, k_blocks = L.K / kBK;
                     for (int nt = 0; nt < tiles_n; ++nt) {
                         const int w_row = nt * BN + (int)rank * (BN / 2);
@@ -248,8 +254,8 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                                 // wait until all 8 epilogue warps have published it (the W tile above is
                                 // already in flight)
                                 c0 = p.prof ? clock64() : 0;
-                                mbar_wait(layer_done, ld_ph);
-                                ld_ph ^= 1;
+                                mbar_wait(&layer_done[sub], (ld_ph >> sub) & 1u);
+                                ld_ph ^= 1u << sub;
                                 if (p.prof) w_layer += clock64() - c0;
                             }
                             tma_load_2d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], kb * kBK, a_row, lead_full);
@@ -257,6 +263,7 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                             if (++s == kStages) { s = 0; ph ^= 1; }
                         }
                     }
+                  }
                 }
             }
             if (p.prof) { p.prof[blockIdx.x * 8 + 0] = w_empty; p.prof[blockIdx.x * 8 + 7] = w_layer; }
@@ -269,9 +276,10 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             int lt = 0;
             long long w_acc = 0, w_full = 0, t_issue = 0;
             const long long k0 = p.prof ? clock64() : 0;
-            for (int t = pair_id; t < tiles_m; t += n_pairs) {
+            for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
+                const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;
                 for (int l = 0; l < nl; ++l) {
-                    const int tiles_n = p.layer[l].N / BN, k_blocks = p.layer[l].K / kBK;
+                    const int tiles_n = p.layer[l].N / BN * n_sub, k_blocks = p.layer[l].K / kBK;   // same order as the producer
                     for (int nt = 0; nt < tiles_n; ++nt, ++lt) {
                         const int acc = lt & 1;
                         long long c0 = p.prof ? clock64() : 0;
@@ -316,10 +324,13 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         uint4* stage = reinterpret_cast<uint4*>(store_stage + (warp - 4) * 4096);
         int lt = 0, dot_round = 0;
         long long w_accfull = 0, t_epi = 0;
-        for (int t = pair_id; t < tiles_m; t += n_pairs) {
-            const int grow_base = t * 2 * kBM + (int)rank * kBM + sub * 32;          // candidate rows
-            const int srow_base = pair_id * 2 * kBM + (int)rank * kBM + sub * 32;    // pair-scratch rows
-            for (int l = 0; l < nl; ++l) {
+        for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
+          const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;
+          for (int l = 0; l < nl; ++l) {
+            for (int st = 0; st < n_sub; ++st) {                                     // the two interleaved tiles of this pair
+                const int t = t0 + st * n_pairs;
+                const int grow_base = t * 2 * kBM + (int)rank * kBM + sub * 32;                 // candidate rows
+                const int srow_base = (pair_id * 2 + st) * 2 * kBM + (int)rank * kBM + sub * 32;   // pair-scratch rows
                 const ChainLayer& L = p.layer[l];
                 const int tiles_n = L.N / BN;
                 const bool dot_epi = L.epi == EPI_HEAD || L.epi == EPI_CROSS_DOT;
@@ -360,9 +371,10 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                     // the next layer, then tell this CTA's producer
                     asm volatile("fence.proxy.async;" ::: "memory");
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(layer_done);
+                    if (lane == 0) mbar_arrive(&layer_done[st]);
                 }
             }
+          }
         }
         if (p.prof && warp == 4 && lane == 0) { p.prof[blockIdx.x * 8 + 5] = w_accfull; p.prof[blockIdx.x * 8 + 6] = t_epi; }
     }
