@@ -51,6 +51,7 @@ enum GemmEpilogue { EPI_RELU = 0, EPI_CROSS = 1, EPI_HEAD = 2, EPI_CROSS_DOT = 3
 
 struct ChainLayer {
     int32_t N, K;              // padded output / reduction widths (N multiple of BN, K of 64)
+    int32_t n_valid;           // columns below this exist in X0 / A (EPI_CROSS* must not read past their rows)
     int32_t epi;
     int32_t a_global;          // A rows addressed by candidate row (first layer) or by pair-scratch row
     const float* bias;         // [N]
@@ -127,7 +128,7 @@ __device__ __forceinline__ void epilogue_half_tile(const ChainParams& p, const C
         if (!cross) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
-        } else if (row_ok) {                                   // x0 * (acc + b) + x_l
+        } else if (row_ok && col0 < L.n_valid) {               // x0 * (acc + b) + x_l (padding columns stay acc + b = 0)
             const int arow = L.a_global ? grow : srow_base + lane;
             const uint4* x0p = reinterpret_cast<const uint4*>(p.x0 + (size_t)grow * p.ldx0 + col0);
             const uint4* xlp = reinterpret_cast<const uint4*>(L.a_ptr + (size_t)arow * L.lda + col0);
