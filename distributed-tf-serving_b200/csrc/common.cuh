@@ -145,6 +145,17 @@ __device__ __forceinline__ uint64_t make_sw128_kmajor_desc(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;                               // SWIZZLE_128B   [61,64)
     return d;
 }
+// Descriptor for a K-major tile in the un-swizzled ("interleaved") canonical layout: core
+// matrices of 8 rows x 16 bytes stored contiguously (128 B); `sbo` bytes from one 8-row group to the
+// next, `lbo` bytes from one 16-byte K group to the next.  Layout type 0 = SWIZZLE_NONE.
+__device__ __forceinline__ uint64_t make_interleaved_kmajor_desc(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);          // start address  [0,14)
+    d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;           // LBO            [16,30)
+    d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;           // SBO            [32,46)
+    d |= (uint64_t)1 << 46;                               // version = 1    [46,48)
+    return d;
+}
 // Instruction descriptor, kind::f16: D=f32, A=B=f16 (format 0) or bf16 (1), both K-major.
 __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n, int ab_format) {
     return (1u << 4) | ((uint32_t)ab_format << 7) | ((uint32_t)ab_format << 10) |
@@ -175,6 +186,10 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_bar_addr) {
 __device__ __forceinline__ void tma_load_2d_pair(void* smem_dst, const CUtensorMap* map, int32_t c0, int32_t c1, uint32_t cluster_bar_addr) {
     asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                  ::"r"(smem_u32(smem_dst)), "l"(map), "r"(cluster_bar_addr), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_pair(void* smem_dst, const CUtensorMap* map, int32_t c0, int32_t c1, int32_t c2, uint32_t cluster_bar_addr) {
+    asm volatile("cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(smem_dst)), "l"(map), "r"(cluster_bar_addr), "r"(c0), "r"(c1), "r"(c2) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t* smem_result, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_result)), "r"(ncols) : "memory");

@@ -83,6 +83,23 @@ int32_t make_map_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t
     return CTR_OK;
 }
 
+// 3-D map over a tile-major activation buffer of `ld` columns (tower.cuh): per 128-row tile the K blocks
+// are contiguous 16 KB runs, described as 32 lines of 512 B; no swizzle, so a box lands in shared memory
+// byte for byte.  Coordinates: (0, 32 * k_block, tile).
+int32_t make_map_tile_major(CUtensorMap* map, const void* base, uint64_t ld, uint64_t n_tiles) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[3] = {256, ld / 2, n_tiles};
+    cuuint64_t strides[2] = {512, (cuuint64_t)kBM * ld * sizeof(__half)};
+    cuuint32_t box[3] = {256, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled (tile-major) failed with CUresult " + std::to_string((int)r));
+    return CTR_OK;
+}
+
 // ------------------------------------------------------------------ weight file (format: DESIGN.md)
 constexpr char kMagic[8] = {'C', 'T', 'R', 'W', '0', '0', '0', '1'};
 constexpr size_t kHeaderBytes = 128;
@@ -206,8 +223,8 @@ struct Slot {
     int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;
     int64_t* d_cids = nullptr; float* d_cwts = nullptr;     // compact lists of a shared-context request (host slots)
     float* d_wide = nullptr; float* d_extra = nullptr; int32_t* d_err = nullptr;
-    __half* buf[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-    int ld[5] = {0, 0, 0, 0, 0};
+    __half* buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int ld[6] = {0, 0, 0, 0, 0, 0};
     std::vector<Chain> chains;
     // pinned staging for pageable callers
     int64_t* h_ids = nullptr; float* h_wts = nullptr; float* h_scores = nullptr; int32_t* h_err = nullptr;
@@ -306,25 +323,15 @@ int32_t set_smem_attr(Kern k, int bytes) {
 int32_t setup_kernel_attrs() {
     int32_t rc;
     if ((rc = set_smem_attr(tower_chain_kernel<256>, ChainCfg<256>::kSmemBytes)) != CTR_OK) return rc;
-    if ((rc = set_smem_attr(tower_chain_kernel<128>, ChainCfg<128>::kSmemBytes)) != CTR_OK) return rc;
     return CTR_OK;
 }
 
-// Output-width alignment of a chain of layers: 256-column tiles move a third less L2 traffic per flop
-// than 128-column ones (cycle counters, one 18944 x 640 x 640 layer: 35.3k cycles of MMA loop with
-// BN = 128, 22.0k padded to 768 with BN = 256), so widths from 384 up are padded to a multiple of 256
-// when every layer of the chain can be.
-int chain_n_align(const std::vector<int>& widths) {
-    for (int n : widths) {
-        const int p128 = round_up(n, 128);
-        if (p128 % 256 != 0 && p128 < 384) return 128;
-    }
-    return 256;
-}
-
-int32_t upload_gemm_layer(const float* W, const float* b, int N, int K, GemmLayer* L, cudaStream_t st, int n_align = 128) {
+// Output widths are padded to 128 columns: the tower walks a layer in 256-column tiles (a third less L2
+// traffic per flop than 128-column ones: 22.0k against 35.3k cycles of MMA loop for one 18944 x 640 x 640
+// layer) and finishes a width that is an odd multiple of 128 with one 128-column tile.
+int32_t upload_gemm_layer(const float* W, const float* b, int N, int K, GemmLayer* L, cudaStream_t st) {
     L->N = N;
-    L->Npad = round_up(N, n_align);
+    L->Npad = round_up(N, 128);
     L->Kpad = round_up(K, kBK);
     float* tmp = nullptr;
     CUDA_TRY(cudaMalloc(&tmp, (size_t)N * K * sizeof(float)));
@@ -427,16 +434,14 @@ int32_t load_model_on_device(ctr_engine* e, int di, const HostWeights& hw) {
         int32_t rc;
         int fan_in = m.d();
         dm.mlp.resize(m.n_hidden);
-        const int mlp_align = chain_n_align(std::vector<int>(m.hidden, m.hidden + m.n_hidden));
-        const int cross_align = chain_n_align(std::vector<int>(1, m.d()));
         for (int l = 0; l < m.n_hidden; ++l) {
             // layer 0 reads X (K padded to d_pad); later layers read the previous padded width
-            if ((rc = upload_gemm_layer(blob + hw.off_mlp_w[l], blob + hw.off_mlp_b[l], m.hidden[l], fan_in, &dm.mlp[l], st, mlp_align)) != CTR_OK) return rc;
+            if ((rc = upload_gemm_layer(blob + hw.off_mlp_w[l], blob + hw.off_mlp_b[l], m.hidden[l], fan_in, &dm.mlp[l], st)) != CTR_OK) return rc;
             fan_in = m.hidden[l];
         }
         dm.cross.resize(m.n_cross);
         for (int l = 0; l < m.n_cross; ++l)
-            if ((rc = upload_gemm_layer(blob + hw.off_cross_w[l], blob + hw.off_cross_b[l], m.d(), m.d(), &dm.cross[l], st, cross_align)) != CTR_OK) return rc;
+            if ((rc = upload_gemm_layer(blob + hw.off_cross_w[l], blob + hw.off_cross_b[l], m.d(), m.d(), &dm.cross[l], st)) != CTR_OK) return rc;
         const float* w_out = blob + hw.off_wout;
         const int h_last = m.hidden[m.n_hidden - 1];
         const int x_part = m.kind == CTR_MODEL_DCN_V2 ? m.d() : 0;
@@ -465,7 +470,8 @@ void free_slot(Slot& s) {
 
 // Builds the chains of a slot from buffers that already exist (no allocation in here: the
 // static-scratch entry point calls this too).
-//   buf[0] X [x_rows, d_pad]   buf[1], buf[2] MLP scratch [scratch_rows, maxn]   buf[3], buf[4] cross scratch [scratch_rows, d_pad]
+//   buf[0] X [x_rows, d_pad] row-major; tile-major pair scratch (tower.cuh), 2 * scratch_rows rows each:
+//   buf[1], buf[2] MLP activations (maxn columns)   buf[3], buf[4] x_l (cross width)   buf[5] copy of x0
 int32_t build_chains(ctr_engine* e, DeviceModel& dm, Slot& s) {
     const ModelDesc& m = e->m;
     s.chains.clear();
@@ -477,15 +483,15 @@ int32_t build_chains(ctr_engine* e, DeviceModel& dm, Slot& s) {
         c.n_layers = (int)layers.size();
         if (c.n_layers > kMaxChain) return fail(CTR_ERR_INVALID, "a chain holds at most 4 layers");
         c.BN = 256;
-        for (auto& L : layers) if (L.Npad % 256) c.BN = 128;
         int a = 0;                                            // buffer id of the current layer's A operand
         for (int l = 0; l < c.n_layers; ++l) {
             const GemmLayer& L = layers[l];
             const bool last = l == c.n_layers - 1;
             const int out = is_cross ? 3 + (l & 1) : 1 + (l & 1);
             if (s.ld[a] < L.Kpad) return fail(CTR_ERR_INVALID, "internal: activation buffer narrower than the layer's K");
-            const int a_rows = a == 0 ? s.x_rows : 2 * s.scratch_rows;     // two interleaved tiles per CTA pair
-            if ((rc = make_map_f16(&c.maps.a[l], s.buf[a], (uint64_t)a_rows, (uint64_t)L.Kpad, (uint64_t)s.ld[a], kBM)) != CTR_OK) return rc;
+            if (a == 0) rc = make_map_f16(&c.maps.a[l], s.buf[0], (uint64_t)s.x_rows, (uint64_t)L.Kpad, (uint64_t)s.ld[0], kBM);
+            else rc = make_map_tile_major(&c.maps.a[l], s.buf[a], (uint64_t)s.ld[a], (uint64_t)(2 * s.scratch_rows / kBM));   // two interleaved tiles per CTA pair
+            if (rc != CTR_OK) return rc;
             if ((rc = make_map_f16(&c.maps.w[l], L.W, (uint64_t)L.Npad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, c.BN / 2)) != CTR_OK) return rc;
             ChainLayer& cl = c.params.layer[l];
             cl.N = L.Npad; cl.K = L.Kpad; cl.a_global = a == 0; cl.bias = L.bias; cl.a_ptr = s.buf[a]; cl.lda = s.ld[a];
@@ -503,6 +509,7 @@ int32_t build_chains(ctr_engine* e, DeviceModel& dm, Slot& s) {
         }
         c.params.n_layers = c.n_layers;
         c.params.x0 = s.buf[0]; c.params.ldx0 = s.ld[0];
+        if (is_cross && c.n_layers > 1) { c.params.x0e = s.buf[5]; c.params.ldx0e = s.ld[5]; }
         c.params.b_out = dm.b_out;
         if (is_cross) {
             c.params.extra_out = s.d_extra;                   // w_x . x_L, consumed by the MLP chain's head
@@ -564,6 +571,7 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
         const int xl_ld = dm.cross.empty() ? dpad : dm.cross.back().Npad;      // cross outputs may be padded past d_pad
         if ((rc = alloc_buf(3, 2 * s.scratch_rows, xl_ld)) != CTR_OK) return rc;
         if ((rc = alloc_buf(4, 2 * s.scratch_rows, xl_ld)) != CTR_OK) return rc;
+        if ((rc = alloc_buf(5, 2 * s.scratch_rows, xl_ld)) != CTR_OK) return rc;
     }
     return build_chains(e, dm, s);
 }
@@ -612,8 +620,7 @@ int32_t launch_chain(const Chain& c, const Slot& s, int n, float* d_scores, int 
     if (!p.extra_out) p.scores = d_scores;
     const int tiles = (n + 2 * kBM - 1) / (2 * kBM);
     const int pairs = std::max(1, std::min(std::min(tiles, num_sms / 2), s.scratch_rows / (2 * kBM)));
-    if (c.BN == 256) tower_chain_kernel<256><<<2 * pairs, kGemmThreads, ChainCfg<256>::kSmemBytes, st>>>(c.maps, p);
-    else tower_chain_kernel<128><<<2 * pairs, kGemmThreads, ChainCfg<128>::kSmemBytes, st>>>(c.maps, p);
+    tower_chain_kernel<256><<<2 * pairs, kGemmThreads, ChainCfg<256>::kSmemBytes, st>>>(c.maps, p);
     CUDA_TRY(cudaGetLastError());
     return CTR_OK;
 }
@@ -675,6 +682,9 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
                 for (int cta = 0; cta < dm.num_sms; cta += 2) { mean += (double)h[cta * 8 + i]; ++cnt; }
                 fprintf(stderr, "  %-22s %12.0f\n", names[i], mean / cnt);
             }
+            double cyc = 0, ns = 0;
+            for (int cta = 0; cta + 1 < dm.num_sms; cta += 2) { cyc += (double)h[cta * 8 + 4]; ns += (double)h[(cta + 1) * 8 + 4]; }
+            if (ns > 0) fprintf(stderr, "  %-22s %12.0f MHz (cycles / globaltimer over the MMA loop)\n", "effective SM clock", cyc / ns * 1000.0);
             cudaFree(d_prof);
         }
     }
@@ -1298,7 +1308,7 @@ int32_t ctr_debug_gemm(ctr_engine* e, int32_t device_index, const float* A, cons
     CUDA_TRY(cudaGetLastError());
     Chain c;
     memset(&c.params, 0, sizeof(c.params));
-    c.BN = (L.Npad % 256 == 0) ? 256 : 128;
+    c.BN = 256;
     c.n_layers = 1;
     if ((rc = make_map_f16(&c.maps.a[0], dA, (uint64_t)Mpad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, kBM)) != CTR_OK) return rc;
     if ((rc = make_map_f16(&c.maps.w[0], L.W, (uint64_t)L.Npad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, c.BN / 2)) != CTR_OK) return rc;
@@ -1392,10 +1402,10 @@ int32_t ctr_debug_gather(ctr_engine* e, int32_t device_index, const int64_t* ids
 constexpr int kStaticMaxCandidates = CTR_STATIC_MAX_CANDIDATES;
 constexpr int kStaticMaxDpad = 768;
 constexpr int kStaticMaxHidden = 1024;
-constexpr size_t kStaticXBytes = (size_t)kStaticMaxCandidates * kStaticMaxDpad * sizeof(__half);     // X, XL0, XL1
+constexpr size_t kStaticXBytes = (size_t)kStaticMaxCandidates * kStaticMaxDpad * sizeof(__half);     // X, XL0, XL1, X0 copy
 constexpr size_t kStaticHBytes = (size_t)kStaticMaxCandidates * kStaticMaxHidden * sizeof(__half);   // H0, H1
 constexpr size_t kStaticVecBytes = (size_t)kStaticMaxCandidates * sizeof(float);                     // wide, extra
-constexpr size_t kStaticScratchBytes = 3 * kStaticXBytes + 2 * kStaticHBytes + 2 * kStaticVecBytes + 256;
+constexpr size_t kStaticScratchBytes = 4 * kStaticXBytes + 2 * kStaticHBytes + 2 * kStaticVecBytes + 256;
 
 static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
 
@@ -1454,13 +1464,14 @@ extern "C" int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, 
     s.buf[2] = reinterpret_cast<__half*>(p); p += kStaticHBytes;
     s.buf[3] = reinterpret_cast<__half*>(p); p += kStaticXBytes;
     s.buf[4] = reinterpret_cast<__half*>(p); p += kStaticXBytes;
+    s.buf[5] = reinterpret_cast<__half*>(p); p += kStaticXBytes;
     s.d_wide = reinterpret_cast<float*>(p); p += kStaticVecBytes;
     s.d_extra = reinterpret_cast<float*>(p); p += kStaticVecBytes;
     s.d_err = reinterpret_cast<int32_t*>(p);
     int maxn = 0;
     for (auto& L : dm.mlp) maxn = std::max(maxn, L.Npad);
     const int xl_ld = dm.cross.empty() ? m.d_pad() : dm.cross.back().Npad;
-    s.ld[0] = m.d_pad(); s.ld[1] = maxn; s.ld[2] = maxn; s.ld[3] = xl_ld; s.ld[4] = xl_ld;
+    s.ld[0] = m.d_pad(); s.ld[1] = maxn; s.ld[2] = maxn; s.ld[3] = xl_ld; s.ld[4] = xl_ld; s.ld[5] = xl_ld;
     if (m.kind != CTR_MODEL_LR) {
         if ((rc = build_chains(e, dm, s)) != CTR_OK) return rc;      // tensor maps over the slices (host-side encode only)
         // the previous call (any engine, any model) may have left anything here: clear what must be zero

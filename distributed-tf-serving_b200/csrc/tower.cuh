@@ -28,10 +28,20 @@
 //              K=16, f16 -> f32), accumulators in the TMEM of both SMs; tcgen05.commit multicasts
 //              "stage free" / "accumulator ready" to both CTAs
 //   warp 2     TMEM allocator (2 accumulators x BN columns: tile i's epilogue overlaps tile i+1's MMAs)
-//   warps 4-11 epilogue: tcgen05.ld -> registers -> bias / activation -> XOR-swizzled warp-private
-//              staging in shared memory -> row-major 16-byte stores (a thread owns a ROW in TMEM;
-//              storing straight from registers costs 32 L1 wavefronts per instruction and made the
-//              first version epilogue-bound: 7.5k cycles per tile against 5.1k of MMA)
+//   warps 4-11 epilogue: tcgen05.ld -> registers -> bias / activation -> 16-byte stores straight from
+//              registers into the TILE-MAJOR scratch (below)
+//
+// Tile-major scratch.  In TMEM a thread owns a ROW of the accumulator, so writing activations
+// row-major costs 32 L1 wavefronts per store instruction (the first version was epilogue-bound: 7.5k
+// cycles per tile against 5.1k of MMA), and DCN-v2's cross epilogue, which also READS x0 and x_l by
+// row, measured ~12k.  Activations between layers are therefore kept in the layout the tensor core
+// reads un-swizzled K-major operands in: per 128-row tile, per group of 8 columns, 128 rows x 16 B
+// contiguous -- [tile][col / 8][row][8 halfs].  A warp's store (32 rows x 16 B of one column group)
+// is one contiguous 512-byte segment; a 64-column K block of a tile is one contiguous 16 KB box for
+// the TMA (3-D map, no swizzle) that lands in shared memory exactly as the MMA descriptor wants it
+// (8 x 16 B core matrices, 128 B between 8-row groups, 2048 B between column groups); and the cross
+// epilogue reads x0 / x_l back with the same coalesced accesses.  Only the first layer's A (the
+// gathered X, written a row per warp by the gather kernel) is row-major with the 128-byte swizzle.
 // Every mbarrier wait is bounded (2 s, then trap): a descriptor or phase bug becomes a CUDA error.
 //
 // Roofline: tensor pipe.  Per K block a CTA pulls 16 KB (A) + BN/2 * 128 B (W half) from L2
@@ -46,6 +56,12 @@ constexpr int kGemmThreads = 384;       // 4 control warps + 8 epilogue warps
 constexpr int kBM = 128;                // rows per CTA; a pair covers 2 * kBM
 constexpr int kBK = 64;                 // 64 halfs = one 128-byte swizzle span
 constexpr int kMaxChain = 4;
+// Strides of the tile-major A operand in shared memory (bring-up switch: -DCTR_A_LBO=128 -DCTR_A_SBO=2048
+// swaps the two descriptor fields).
+#ifndef CTR_A_LBO
+#define CTR_A_LBO 2048     // bytes from one 8-column (16-byte) group to the next
+#define CTR_A_SBO 128      // bytes from one 8-row core matrix to the next
+#endif
 
 enum GemmEpilogue { EPI_RELU = 0, EPI_CROSS = 1, EPI_HEAD = 2, EPI_CROSS_DOT = 3 };
 
@@ -53,13 +69,13 @@ struct ChainLayer {
     int32_t N, K;              // padded output / reduction widths (N multiple of BN, K of 64)
     int32_t n_valid;           // columns below this exist in X0 / A (EPI_CROSS* must not read past their rows)
     int32_t epi;
-    int32_t a_global;          // A rows addressed by candidate row (first layer) or by pair-scratch row
+    int32_t a_global;          // 1: A is row-major [M, lda] addressed by candidate row (first layer); 0: tile-major pair scratch
     const float* bias;         // [N]
     const __half* a_ptr;       // the A operand as a plain pointer (EPI_CROSS* reads x_l from it)
-    int32_t lda;
-    __half* out;               // pair-scratch output [n_pairs * 256, ldo] (EPI_RELU / EPI_CROSS)
+    int32_t lda;               // row stride (row-major) or column count (tile-major) of A
+    __half* out;               // tile-major pair scratch, ldo columns (EPI_RELU / EPI_CROSS)
     int32_t ldo;
-    int32_t out_global;        // test hook: store by candidate row instead of pair-scratch row
+    int32_t out_global;        // test hook: store row-major by candidate row instead (slow path)
     const float* w_out;        // [N] (dot epilogues)
 };
 
@@ -67,8 +83,10 @@ struct ChainParams {
     int32_t M;                 // candidates in this launch
     int32_t n_layers;
     ChainLayer layer[kMaxChain];
-    const __half* x0;          // [M, ldx0] gathered activations (EPI_CROSS*)
+    const __half* x0;          // [M, ldx0] gathered activations, row-major (EPI_CROSS* of the first layer)
     int32_t ldx0;
+    __half* x0e;               // tile-major copy of x0 in the pair scratch, written by the first cross layer's
+    int32_t ldx0e;             //   epilogue and read by the later ones (nullptr: single-layer chain)
     const float* wide;         // [M] or nullptr
     const float* extra_in;     // [M] or nullptr
     float b_out;
@@ -87,56 +105,89 @@ struct ChainCfg {
     static constexpr int kABytes = kBM * kBK * 2;                 // 16 KB: this CTA's 128 rows
     static constexpr int kBBytes = (BN / 2) * kBK * 2;            // 16 KB / 8 KB: this CTA's half of the W tile
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = BN == 256 ? 5 : 6;
+    static constexpr int kStages = BN == 256 ? 6 : 8;
     static constexpr int kTmemCols = 2 * BN;
-    static constexpr int kStoreStageBytes = 8 * 4096;             // 8 epilogue warps x (32 rows x 128 B)
-    static constexpr int kSmemBytes = kStages * kStageBytes + kStoreStageBytes + 1024 + 256;
+    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 + 256;
 };
 
-// Drains one half (BN/2 columns) of a 128-row accumulator tile for the calling warp's 32 rows.
-//   grow_base: candidate row of the warp's first row (guards, x0, wide); srow_base: scratch row.
-template <int BN>
-__device__ __forceinline__ void epilogue_half_tile(const ChainParams& p, const ChainLayer& L, uint32_t taddr, int grow_base,
-                                                   int srow_base, int lane, int n0, float& dot, uint4* stage) {
-    constexpr int kChunks = (BN / 2) / 32;
-    static_assert(kChunks % 2 == 0, "two 32-column chunks per staging round");
+// Offset (in halfs) of the 16-byte unit (row r of 128, column group g) of tile `tile` in a tile-major
+// buffer of `ld` columns.
+__device__ __forceinline__ size_t tile_major_off(int tile, int ld, int g, int r) {
+    return (size_t)tile * (size_t)(kBM * ld) + (size_t)g * (kBM * 8) + (size_t)r * 8;
+}
+
+// x0 and x_l pieces (4 column groups x 16 B each) of one 32-column chunk of a cross epilogue
+struct CrossRegs { uint4 a[4], b[4]; };
+
+// Issues the loads of one chunk's cross operands.  They do not depend on the accumulator, so the caller
+// has them in flight one chunk ahead (also across N tiles): with 8 epilogue warps per SM nothing else
+// hides their L2 round trip.
+__device__ __forceinline__ void load_cross(const ChainParams& p, const ChainLayer& L, bool row_ok, int grow, int stile, int r,
+                                           int col0, CrossRegs& x) {
+    if (!row_ok || col0 >= L.n_valid) return;                  // same predicate as the consumer's
+    if (L.a_global) {                                          // first cross layer: x_l = x0, row-major (gather output)
+        const uint4* x0p = reinterpret_cast<const uint4*>(p.x0 + (size_t)grow * p.ldx0 + col0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) x.a[j] = __ldg(x0p + j);
+    } else {                                                   // written by this very thread one layer ago: plain loads
+        const __half* x0p = p.x0e + tile_major_off(stile, p.ldx0e, col0 >> 3, r);
+        const __half* xlp = L.a_ptr + tile_major_off(stile, L.lda, col0 >> 3, r);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            x.a[j] = *reinterpret_cast<const uint4*>(x0p + j * (kBM * 8));
+            x.b[j] = *reinterpret_cast<const uint4*>(xlp + j * (kBM * 8));
+        }
+    }
+}
+
+// Drains kChunks x 32 columns (from column n0) of a 128-row accumulator tile for the calling warp's 32 rows.
+//   grow: candidate row of this thread (guards, row-major x0, wide); stile / r: its 128-row scratch
+//   tile and its row in it.  Cross epilogues: x[0] holds the first chunk's operands on entry and, if
+//   next_n0 >= 0, the first chunk's of the tile starting at column next_n0 on exit.
+template <int kChunks>
+__device__ __forceinline__ void epilogue_tile(const ChainParams& p, const ChainLayer& L, uint32_t taddr, int grow,
+                                              int stile, int r, int n0, int next_n0, CrossRegs (&x)[2], float& dot) {
+    static_assert(kChunks % 2 == 0, "the operand double buffer returns to slot 0 at a tile boundary");
     const int epi = L.epi;
     const bool cross = epi == EPI_CROSS || epi == EPI_CROSS_DOT;
     const bool dot_epi = epi == EPI_HEAD || epi == EPI_CROSS_DOT;
-    const int grow = grow_base + lane;
     const bool row_ok = grow < p.M;
-    uint32_t r[2][32];
-    tmem_ld32(taddr, r[0]);
+    uint32_t rr[32];
+    tmem_ld32(taddr, rr);
 #pragma unroll
     for (int c = 0; c < kChunks; ++c) {
         const int col0 = n0 + c * 32;
-        float4 bv[8];                                          // same address in every lane: broadcast, L1-resident
-        const float4* bias4 = reinterpret_cast<const float4*>(L.bias + col0);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) bv[j] = __ldg(bias4 + j);
-        tmem_ld_wait();                                        // chunk c has landed in r[c & 1]
-        if (c + 1 < kChunks) tmem_ld32(taddr + (c + 1) * 32, r[(c + 1) & 1]);   // overlaps the math below
-        const uint32_t* rc = r[c & 1];
+        if (cross) {
+            if (c + 1 < kChunks) load_cross(p, L, row_ok, grow, stile, r, col0 + 32, x[(c + 1) & 1]);
+            else if (next_n0 >= 0) load_cross(p, L, row_ok, grow, stile, r, next_n0, x[0]);
+        }
+        tmem_ld_wait();                                        // chunk c has landed
         float v[32];
+        const float4* bias4 = reinterpret_cast<const float4*>(L.bias + col0);   // same address in every lane: broadcast
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            v[4 * j + 0] = __uint_as_float(rc[4 * j + 0]) + bv[j].x;
-            v[4 * j + 1] = __uint_as_float(rc[4 * j + 1]) + bv[j].y;
-            v[4 * j + 2] = __uint_as_float(rc[4 * j + 2]) + bv[j].z;
-            v[4 * j + 3] = __uint_as_float(rc[4 * j + 3]) + bv[j].w;
+            const float4 bv = __ldg(bias4 + j);
+            v[4 * j + 0] = __uint_as_float(rr[4 * j + 0]) + bv.x;
+            v[4 * j + 1] = __uint_as_float(rr[4 * j + 1]) + bv.y;
+            v[4 * j + 2] = __uint_as_float(rr[4 * j + 2]) + bv.z;
+            v[4 * j + 3] = __uint_as_float(rr[4 * j + 3]) + bv.w;
         }
+        if (c + 1 < kChunks) tmem_ld32(taddr + (c + 1) * 32, rr);   // rr is free again: the load overlaps the rest of this chunk
         if (!cross) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         } else if (row_ok && col0 < L.n_valid) {               // x0 * (acc + b) + x_l (padding columns stay acc + b = 0)
-            const int arow = L.a_global ? grow : srow_base + lane;
-            const uint4* x0p = reinterpret_cast<const uint4*>(p.x0 + (size_t)grow * p.ldx0 + col0);
-            const uint4* xlp = reinterpret_cast<const uint4*>(L.a_ptr + (size_t)arow * L.lda + col0);
+            const CrossRegs& xc = x[c & 1];
+            if (L.a_global && p.x0e) {                         // keep x0 where the later layers read it coalesced
+                __half* x0w = p.x0e + tile_major_off(stile, p.ldx0e, col0 >> 3, r);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(x0w + j * (kBM * 8)) = xc.a[j];
+            }
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                const uint4 a = __ldg(x0p + j), b = *(xlp + j);
-                const __half2* ah = reinterpret_cast<const __half2*>(&a);
-                const __half2* bh = reinterpret_cast<const __half2*>(&b);
+                const uint4 xl = L.a_global ? xc.a[j] : xc.b[j];
+                const __half2* ah = reinterpret_cast<const __half2*>(&xc.a[j]);
+                const __half2* bh = reinterpret_cast<const __half2*>(&xl);
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float2 af = __half22float2(ah[e]), bf = __half22float2(bh[e]);
@@ -155,28 +206,16 @@ __device__ __forceinline__ void epilogue_half_tile(const ChainParams& p, const C
                 dot = fmaf(v[4 * j + 2], wv.z, dot);
                 dot = fmaf(v[4 * j + 3], wv.w, dot);
             }
-        } else {
-            // this thread's 32 columns -> 4 x 16 B into its row of the staging block (swizzled: conflict-free)
+        } else if (row_ok) {
+            // this thread's 32 columns = 4 column groups x 16 B; the warp's 32 rows of a group are contiguous
+            __half* o = L.out_global ? L.out + (size_t)grow * L.ldo + col0 : L.out + tile_major_off(stile, L.ldo, col0 >> 3, r);
+            const int step = L.out_global ? 8 : kBM * 8;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 __half2 h[4];
 #pragma unroll
                 for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[8 * j + 2 * e], v[8 * j + 2 * e + 1]);
-                const int lc = (c & 1) * 4 + j;
-                stage[lane * 8 + (lc ^ (lane & 7))] = *reinterpret_cast<const uint4*>(h);
-            }
-            if (c & 1) {
-                __syncwarp();
-                const int colbase = n0 + (c - 1) * 32;               // first of the 64 staged columns
-                const int cc = lane & 7;
-#pragma unroll
-                for (int it = 0; it < 8; ++it) {
-                    const int rr = it * 4 + (lane >> 3);
-                    const uint4 val = stage[rr * 8 + (cc ^ (rr & 7))];
-                    if (grow_base + rr < p.M)
-                        *reinterpret_cast<uint4*>(L.out + (size_t)((L.out_global ? grow_base : srow_base) + rr) * L.ldo + colbase + cc * 8) = val;
-                }
-                __syncwarp();
+                *reinterpret_cast<uint4*>(o + j * step) = *reinterpret_cast<const uint4*>(h);
             }
         }
     }
@@ -192,8 +231,7 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint8_t* smem_a = smem;
     uint8_t* smem_b = smem + kStages * Cfg::kABytes;
-    uint8_t* store_stage = smem + kStages * Cfg::kStageBytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(store_stage + Cfg::kStoreStageBytes);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kStages * Cfg::kStageBytes);
     uint64_t* full_bar = bars;                     // [kStages] used in the leader: both CTAs' TMA -> MMA
     uint64_t* empty_bar = bars + kStages;          // [kStages] in each CTA: MMA -> that CTA's producer
     uint64_t* acc_full = bars + 2 * kStages;       // [2] in each CTA: MMA -> that CTA's epilogue
@@ -239,10 +277,12 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                   for (int sub = 0; sub < n_sub; ++sub) {
                     const ChainLayer& L = p.layer[l];
                     const int t = t0 + sub * n_pairs;
-                    const int a_row = (L.a_global ? t : pair_id * 2 + sub) * 2 * kBM + (int)rank * kBM;
-                    const int tiles_n = L.N / BN, k_blocks = L.K / kBK;
+                    const int a_row = t * 2 * kBM + (int)rank * kBM;          // row-major A: candidate rows
+                    const int a_tile = (pair_id * 2 + sub) * 2 + (int)rank;   // tile-major A: this CTA's scratch tile
+                    const int tiles_n = (L.N + BN - 1) / BN, k_blocks = L.K / kBK;
                     for (int nt = 0; nt < tiles_n; ++nt) {
-                        const int w_row = nt * BN + (int)rank * (BN / 2);
+                        // the last tile of a layer may be 128 wide: each CTA then feeds the first 64 rows of its box
+                        const int w_row = nt * BN + (int)rank * (min(BN, L.N - nt * BN) / 2);
                         for (int kb = 0; kb < k_blocks; ++kb) {
                             long long c0 = p.prof ? clock64() : 0;
                             mbar_wait(&empty_bar[s], ph ^ 1);
@@ -259,7 +299,8 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                                 ld_ph ^= 1u << sub;
                                 if (p.prof) w_layer += clock64() - c0;
                             }
-                            tma_load_2d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], kb * kBK, a_row, lead_full);
+                            if (L.a_global) tma_load_2d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], kb * kBK, a_row, lead_full);
+                            else tma_load_3d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], 0, kb * 32, a_tile, lead_full);   // 16 KB contiguous
                             if (!leader) mbar_arrive_cluster(lead_full);
                             if (++s == kStages) { s = 0; ph ^= 1; }
                         }
@@ -272,17 +313,20 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
         if (leader && lane == 0) {
-            constexpr uint32_t idesc = make_idesc_f16(2 * kBM, BN, /*f16*/ 0);
             int s = 0; uint32_t ph = 0;
             int lt = 0;
             long long w_acc = 0, w_full = 0, t_issue = 0;
             const long long k0 = p.prof ? clock64() : 0;
+            const uint64_t ns0 = p.prof ? globaltimer_ns() : 0;
             for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
                 const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;
                 for (int l = 0; l < nl; ++l) {
-                    const int tiles_n = p.layer[l].N / BN * n_sub, k_blocks = p.layer[l].K / kBK;   // same order as the producer
+                    const int tiles_l = (p.layer[l].N + BN - 1) / BN, k_blocks = p.layer[l].K / kBK;
+                    const int tiles_n = tiles_l * n_sub;                                            // same order as the producer
+                    const bool a_rowmajor = p.layer[l].a_global != 0;
                     for (int nt = 0; nt < tiles_n; ++nt, ++lt) {
                         const int acc = lt & 1;
+                        const uint32_t idesc = make_idesc_f16(2 * kBM, min(BN, p.layer[l].N - (nt % tiles_l) * BN), /*f16*/ 0);
                         long long c0 = p.prof ? clock64() : 0;
                         mbar_wait(&acc_empty[acc], ((lt >> 1) & 1) ^ 1);      // both CTAs' epilogues drained it
                         if (p.prof) w_acc += clock64() - c0;
@@ -298,7 +342,9 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
 #pragma unroll
                             for (int k = 0; k < kBK / 16; ++k) {
                                 // advancing K by 16 halfs = 32 bytes inside the 128-byte swizzle span
-                                const uint64_t da = make_sw128_kmajor_desc(a_addr + k * 32);
+                                // tile-major A: a K step of 16 halfs is two column groups of 2048 B
+                                const uint64_t da = a_rowmajor ? make_sw128_kmajor_desc(a_addr + k * 32)
+                                                               : make_interleaved_kmajor_desc(a_addr + k * 4096, CTR_A_LBO, CTR_A_SBO);
                                 const uint64_t db = make_sw128_kmajor_desc(b_addr + k * 32);
                                 umma_f16_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
                             }
@@ -313,6 +359,7 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             if (p.prof) {
                 p.prof[blockIdx.x * 8 + 1] = w_acc; p.prof[blockIdx.x * 8 + 2] = w_full; p.prof[blockIdx.x * 8 + 3] = t_issue;
                 p.prof[blockIdx.x * 8 + 4] = clock64() - k0;
+                p.prof[(blockIdx.x + 1) * 8 + 4] = (long long)(globaltimer_ns() - ns0);     // peer's slot: wall time of the same loop
             }
         }
     } else if (warp >= 4) {
@@ -321,29 +368,34 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         // sub-partition and split the tile's columns in halves.
         const int sub = warp & 3;
         const int half = (warp - 4) >> 2;
-        constexpr int kHalfCols = BN / 2;
-        uint4* stage = reinterpret_cast<uint4*>(store_stage + (warp - 4) * 4096);
         int lt = 0, dot_round = 0;
+        CrossRegs x[2];
         long long w_accfull = 0, t_epi = 0;
         for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
           const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;
           for (int l = 0; l < nl; ++l) {
             for (int st = 0; st < n_sub; ++st) {                                     // the two interleaved tiles of this pair
                 const int t = t0 + st * n_pairs;
-                const int grow_base = t * 2 * kBM + (int)rank * kBM + sub * 32;                 // candidate rows
-                const int srow_base = (pair_id * 2 + st) * 2 * kBM + (int)rank * kBM + sub * 32;   // pair-scratch rows
+                const int grow = t * 2 * kBM + (int)rank * kBM + sub * 32 + lane;        // this thread's candidate row
+                const int stile = (pair_id * 2 + st) * 2 + (int)rank;                     // this CTA's 128-row scratch tile
                 const ChainLayer& L = p.layer[l];
-                const int tiles_n = L.N / BN;
+                const int tiles_n = (L.N + BN - 1) / BN;
                 const bool dot_epi = L.epi == EPI_HEAD || L.epi == EPI_CROSS_DOT;
+                const bool cross = L.epi == EPI_CROSS || L.epi == EPI_CROSS_DOT;
+                const int r = sub * 32 + lane;
                 float dot = 0.f;
+                if (cross) load_cross(p, L, grow < p.M, grow, stile, r, half * (min(BN, L.N) / 2), x[0]);
                 for (int nt = 0; nt < tiles_n; ++nt, ++lt) {
                     const int acc = lt & 1;
+                    const int hc = min(BN, L.N - nt * BN) / 2;                 // columns per warp: 128, or 64 in a narrow last tile
+                    const int next_n0 = nt + 1 < tiles_n ? (nt + 1) * BN + half * (min(BN, L.N - (nt + 1) * BN) / 2) : -1;
                     const long long c0 = p.prof ? clock64() : 0;
                     mbar_wait(&acc_full[acc], (lt >> 1) & 1);
                     const long long c1 = p.prof ? clock64() : 0;
                     tc_fence_after();
-                    const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN + half * kHalfCols;
-                    epilogue_half_tile<BN>(p, L, taddr, grow_base, srow_base, lane, nt * BN + half * kHalfCols, dot, stage);
+                    const uint32_t taddr = tmem_base + ((uint32_t)(sub * 32) << 16) + acc * BN + half * hc;
+                    if (BN == 256 && hc == 128) epilogue_tile<4>(p, L, taddr, grow, stile, r, nt * BN + half * hc, next_n0, x, dot);
+                    else epilogue_tile<2>(p, L, taddr, grow, stile, r, nt * BN + half * hc, next_n0, x, dot);
                     // TMEM reads of this accumulator are done: hand it back to the MMA warp (in the leader)
                     tc_fence_before();
                     __syncwarp();
@@ -356,7 +408,6 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                     ++dot_round;
                     if (half == 1) dot_part[buf * kBM + sub * 32 + lane] = dot;
                     asm volatile("bar.sync %0, 64;" ::"r"(1 + sub) : "memory");
-                    const int grow = grow_base + lane;
                     if (half == 0 && grow < p.M) {
                         float z = dot + dot_part[buf * kBM + sub * 32 + lane];
                         if (p.extra_out) p.extra_out[grow] = z;
