@@ -172,7 +172,7 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
  * memory or enter the driver's allocator on the request path: processes whose HBM is already
  * owned in full by another pool, and latency-critical threads for which a cudaMalloc (which can
  * stall every stream of the device) is not acceptable.  The intermediate activations live in
- * one fixed __device__ array inside the library image (about 8.5 MB, resident on every GPU that
+ * one fixed __device__ array inside the library image (about 10.5 MB, resident on every GPU that
  * loads the library until the process exits), so a call handles at most
  * CTR_STATIC_MAX_CANDIDATES candidates (models with d_padded <= 768, hidden widths <= 1024);
  * larger requests fail with CTR_ERR_CAPACITY.  The call itself performs no cudaMalloc / cudaFree.
