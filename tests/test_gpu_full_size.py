@@ -1,0 +1,127 @@
+"""GPU parity at BASELINE.json's full size (config 2: Wide&Deep, 13 dense + 26 sparse fields,
+dim 16, 2^22 rows per sparse field = 109 M rows = 14 GB fp32 table, 10 000-candidate requests, and
+the bench's 64-request step of 640 000 candidates).
+
+The oracle cannot score 640 000 candidates in seconds, so the checks are the size-independent
+properties of the path plus a sampled comparison:
+  * a random sample of the scores against the oracle (fp64 master and kernel-contract emulation);
+  * candidates are independent: permuting the request permutes the scores bit for bit, duplicated
+    candidates get identical scores, and splitting the request anywhere (DCNClient.java:46-55 does
+    it at N/P) and concatenating in order (DCNClient.java:161-164) changes nothing;
+  * the sorted response (DCNClient.java:195) is ascending in Float.compareTo order and is a
+    permutation of the unsorted one;
+  * host path, device-resident path and the no-allocation path agree bit for bit."""
+import numpy as np
+import pytest
+
+from conftest import make_case
+
+pytestmark = pytest.mark.gpu
+
+TOL_F16 = 2e-3      # probabilities, 16-bit tower vs the fp64 master (north star)
+TOL_F16_EMU = 3e-4  # vs the oracle's emulation of the kernel's rounding points
+ROWS_PER_FIELD = 1 << 22
+
+
+@pytest.fixture(scope="module")
+def om():
+    from oracle import model
+    return model
+
+
+@pytest.fixture(scope="module")
+def full(lib_built, om, tmp_path_factory):
+    """Engine with the full-size model loaded once for the module."""
+    from dtfs_b200 import binding
+    w = make_case(om.WIDE_DEEP, hidden=(1024, 512, 256), rows_per_field=ROWS_PER_FIELD)
+    path = str(tmp_path_factory.mktemp("full") / "weights.ctrw")
+    om.save_weights(w, path)
+    e = binding.Engine(max_candidates=10000)
+    info = e.load_weights(path)
+    assert info.num_rows == om.criteo_num_rows(13, 26, ROWS_PER_FIELD)
+    assert info.table_bytes_per_device == info.num_rows * 128
+    yield e, w
+    e.close()
+
+
+def test_request_of_10000_sampled_against_the_oracle(full, om):
+    e, w = full
+    n = 10000
+    ids, wts = om.criteo_inputs(n, seed=77, rows_per_field=ROWS_PER_FIELD)
+    got = e.predict(ids, wts).copy()
+    assert got.shape == (n,) and np.all(np.isfinite(got)) and got.min() >= 0 and got.max() <= 1
+    pick = np.random.default_rng(5).choice(n, 384, replace=False)
+    pick = np.concatenate([pick, [0, n - 1]])
+    p64 = om.forward(w, ids[pick], wts[pick], "fp64")
+    pemu = om.forward(w, ids[pick], wts[pick], "f16")
+    assert np.std(om.forward_logits(w, ids[pick], wts[pick], "fp64")) > 0.5
+    assert np.abs(got[pick] - pemu).max() <= TOL_F16_EMU
+    assert np.abs(got[pick] - p64).max() <= TOL_F16
+
+
+def test_candidates_are_independent(full, om):
+    e, w = full
+    n = 10000
+    ids, wts = om.criteo_inputs(n, seed=78, rows_per_field=ROWS_PER_FIELD)
+    base = e.predict(ids, wts).copy()
+    # permutation equivariance
+    perm = np.random.default_rng(6).permutation(n)
+    assert np.array_equal(e.predict(np.ascontiguousarray(ids[perm]), np.ascontiguousarray(wts[perm])), base[perm])
+    # duplicates
+    ids2, wts2 = ids.copy(), wts.copy()
+    ids2[1::2], wts2[1::2] = ids2[0::2], wts2[0::2]
+    dup = e.predict(ids2, wts2)
+    assert np.array_equal(dup[0::2], dup[1::2]) and np.array_equal(dup[0::2], base[0::2])
+    # split anywhere + ordered concat (the reference's own split points and two ragged ones)
+    from dtfs_b200 import binding
+    for parts in (2, 3, 7):
+        merged = np.concatenate([e.predict(np.ascontiguousarray(ids[a:b]), np.ascontiguousarray(wts[a:b]))
+                                 for a, b in binding.partition_bounds(n, parts)])
+        assert np.array_equal(merged, base), parts
+    for cut in (1, 4097):
+        merged = np.concatenate([e.predict(np.ascontiguousarray(ids[:cut]), np.ascontiguousarray(wts[:cut])),
+                                 e.predict(np.ascontiguousarray(ids[cut:]), np.ascontiguousarray(wts[cut:]))])
+        assert np.array_equal(merged, base), cut
+
+
+def test_sorted_response_properties(full, om):
+    from oracle import dcn_client as oc
+    e, w = full
+    n = 10000
+    ids, wts = om.criteo_inputs(n, seed=79, rows_per_field=ROWS_PER_FIELD)
+    base = e.predict(ids, wts).copy()
+    s, idx = e.predict_sorted(ids, wts)
+    assert np.array_equal(np.sort(idx), np.arange(n))            # a permutation of the candidates
+    assert np.array_equal(base[idx], s)                          # of exactly the unsorted scores
+    key = oc.java_float_sort_key(s)
+    assert np.all(key[:-1] <= key[1:])                           # ascending in Float.compareTo order
+    assert np.array_equal(s, oc.java_float_sort(base))
+
+
+def test_bench_step_of_640000_device_resident(full, om):
+    """The bench's step: 64 requests of 10 000 candidates in one device-resident call."""
+    import torch
+    e, w = full
+    n_req, n = 64, 10000
+    ids, wts = om.criteo_inputs(n_req * n, seed=80, rows_per_field=ROWS_PER_FIELD)
+    d_ids, d_wts = torch.from_numpy(ids).cuda(), torch.from_numpy(wts).cuda()
+    d_out = torch.empty(n_req * n, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    e.score_device(d_ids.data_ptr(), d_wts.data_ptr(), n_req * n, d_out.data_ptr())
+    allp = d_out.cpu().numpy()
+    assert np.all(np.isfinite(allp))
+    # request 0, request 63 and one from the middle through the host path: bit-identical
+    for r in (0, 37, 63):
+        assert np.array_equal(e.predict(ids[r * n:(r + 1) * n], wts[r * n:(r + 1) * n]), allp[r * n:(r + 1) * n]), r
+    # a sample across the whole step against the oracle
+    pick = np.random.default_rng(7).choice(n_req * n, 256, replace=False)
+    assert np.abs(allp[pick] - om.forward(w, ids[pick], wts[pick], "f16")).max() <= TOL_F16_EMU
+    assert np.abs(allp[pick] - om.forward(w, ids[pick], wts[pick], "fp64")).max() <= TOL_F16
+    # a second call gives the same bits (no state carried in the scratch), and so does the fixed-scratch path
+    d_out2 = torch.empty_like(d_out)
+    e.score_device(d_ids.data_ptr(), d_wts.data_ptr(), n_req * n, d_out2.data_ptr())
+    assert np.array_equal(d_out2.cpu().numpy(), allp)
+    d_out3 = torch.empty(1024, dtype=torch.float32, device="cuda")
+    e.score_device_static(d_ids.data_ptr(), d_wts.data_ptr(), 1024, d_out3.data_ptr())
+    torch.cuda.synchronize()
+    assert np.array_equal(d_out3.cpu().numpy(), allp[:1024])
