@@ -268,7 +268,9 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
 
     if (warp == 0) {
         // ===================== TMA producer (both CTAs) =====================
-        if (lane == 0) {
+        // The whole warp walks the loop (so addresses and coordinates stay in uniform registers) and one
+        // elected lane issues.
+        {
             int s = 0; uint32_t ph = 0, ld_ph = 0;
             long long w_empty = 0, w_layer = 0;
             for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
@@ -288,8 +290,11 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                             mbar_wait(&empty_bar[s], ph ^ 1);
                             if (p.prof) w_empty += clock64() - c0;
                             const uint32_t lead_full = map_to_cta(smem_u32(&full_bar[s]), 0);
-                            if (leader) mbar_expect_tx(&full_bar[s], 2 * Cfg::kStageBytes);      // bytes of both CTAs
-                            tma_load_2d_pair(smem_b + s * Cfg::kBBytes, &maps.w[l], kb * kBK, w_row, lead_full);
+                            const bool issuer = elect_one();
+                            if (issuer) {
+                                if (leader) mbar_expect_tx(&full_bar[s], 2 * Cfg::kStageBytes);  // bytes of both CTAs
+                                tma_load_2d_pair(smem_b + s * Cfg::kBBytes, &maps.w[l], kb * kBK, w_row, lead_full);
+                            }
                             if (l > 0 && nt == 0 && kb == 0) {
                                 // A of this layer is what this CTA's epilogue stored for the previous layer:
                                 // wait until all 8 epilogue warps have published it (the W tile above is
@@ -299,20 +304,26 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                                 ld_ph ^= 1u << sub;
                                 if (p.prof) w_layer += clock64() - c0;
                             }
-                            if (L.a_global) tma_load_2d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], kb * kBK, a_row, lead_full);
-                            else tma_load_3d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], 0, kb * 32, a_tile, lead_full);   // 16 KB contiguous
-                            if (!leader) mbar_arrive_cluster(lead_full);
+                            if (issuer) {
+                                if (L.a_global) tma_load_2d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], kb * kBK, a_row, lead_full);
+                                else tma_load_3d_pair(smem_a + s * Cfg::kABytes, &maps.a[l], 0, kb * 32, a_tile, lead_full);   // 16 KB contiguous
+                                if (!leader) mbar_arrive_cluster(lead_full);
+                            }
+                            __syncwarp();
                             if (++s == kStages) { s = 0; ph ^= 1; }
                         }
                     }
                   }
                 }
             }
-            if (p.prof) { p.prof[blockIdx.x * 8 + 0] = w_empty; p.prof[blockIdx.x * 8 + 7] = w_layer; }
+            if (p.prof && lane == 0) { p.prof[blockIdx.x * 8 + 0] = w_empty; p.prof[blockIdx.x * 8 + 7] = w_layer; }
         }
     } else if (warp == 1) {
         // ===================== MMA issuer (leader CTA only) =====================
-        if (leader && lane == 0) {
+        // Warp-uniform loop, one elected lane issues: issued from inside a single-lane branch the
+        // descriptors sit in per-thread registers and every tcgen05.mma pays a ~30-instruction
+        // move-to-uniform-register loop, which leaves the issuer no run-ahead over the tensor pipe.
+        if (leader) {
             int s = 0; uint32_t ph = 0;
             int lt = 0;
             long long w_acc = 0, w_full = 0, t_issue = 0;
@@ -339,24 +350,27 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                             tc_fence_after();
                             const uint32_t a_addr = smem_u32(smem_a + s * Cfg::kABytes);
                             const uint32_t b_addr = smem_u32(smem_b + s * Cfg::kBBytes);
+                            // advancing K by 16 halfs = 32 bytes inside the 128-byte swizzle span; in the
+                            // tile-major A it is two column groups of 2048 B (start-address field: 16-byte units)
+                            const uint64_t da0 = a_rowmajor ? make_sw128_kmajor_desc(a_addr) : make_interleaved_kmajor_desc(a_addr, CTR_A_LBO, CTR_A_SBO);
+                            const uint64_t da_step = a_rowmajor ? (32 >> 4) : (4096 >> 4);
+                            const uint64_t db0 = make_sw128_kmajor_desc(b_addr);
+                            if (elect_one()) {
 #pragma unroll
-                            for (int k = 0; k < kBK / 16; ++k) {
-                                // advancing K by 16 halfs = 32 bytes inside the 128-byte swizzle span
-                                // tile-major A: a K step of 16 halfs is two column groups of 2048 B
-                                const uint64_t da = a_rowmajor ? make_sw128_kmajor_desc(a_addr + k * 32)
-                                                               : make_interleaved_kmajor_desc(a_addr + k * 4096, CTR_A_LBO, CTR_A_SBO);
-                                const uint64_t db = make_sw128_kmajor_desc(b_addr + k * 32);
-                                umma_f16_pair(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                                for (int k = 0; k < kBK / 16; ++k)
+                                    umma_f16_pair(d_tmem, da0 + k * da_step, db0 + k * (32 >> 4), idesc, (kb | k) != 0 ? 1u : 0u);
+                                umma_commit_pair(&empty_bar[s]);              // stage free in both CTAs
                             }
-                            umma_commit_pair(&empty_bar[s]);                  // stage free in both CTAs
+                            __syncwarp();
                             if (p.prof) { w_full += c1 - c0; t_issue += clock64() - c1; }
                             if (++s == kStages) { s = 0; ph ^= 1; }
                         }
-                        umma_commit_pair(&acc_full[acc]);                     // accumulator ready in both CTAs
+                        if (elect_one()) umma_commit_pair(&acc_full[acc]);    // accumulator ready in both CTAs
+                        __syncwarp();
                     }
                 }
             }
-            if (p.prof) {
+            if (p.prof && lane == 0) {
                 p.prof[blockIdx.x * 8 + 1] = w_acc; p.prof[blockIdx.x * 8 + 2] = w_full; p.prof[blockIdx.x * 8 + 3] = t_issue;
                 p.prof[blockIdx.x * 8 + 4] = clock64() - k0;
                 p.prof[(blockIdx.x + 1) * 8 + 4] = (long long)(globaltimer_ns() - ns0);     // peer's slot: wall time of the same loop
