@@ -9,6 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libctr_b200.so")
 HOST_DEMO = os.path.join(HERE, "dcn_client_host")
+STREAM_SWEEP = os.path.join(HERE, "stream_sweep_host")
 SOURCES = ["engine.cu", "common.cuh", "gather.cuh", "tower.cuh", "sort.cuh", "wire.hpp", os.path.join("..", "..", "include", "ctr_engine.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
@@ -48,6 +49,16 @@ def build_host_demo(force: bool = False) -> str:
     return HOST_DEMO
 
 
+def build_stream_sweep(force: bool = False) -> str:
+    """C++ driver of BASELINE config 5 (request stream sweep: closed loop + open-loop Poisson arrivals)."""
+    src = os.path.join(CSRC, "stream_sweep_host.cpp")
+    if force or _stale(STREAM_SWEEP, [src, os.path.join(CSRC, "..", "..", "include", "ctr_engine.h")]):
+        cxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+        subprocess.check_call([cxx, "-O2", "-std=c++17", "-pthread", "-Wall", "-o", STREAM_SWEEP, src, "-ldl"], cwd=CSRC)
+    return STREAM_SWEEP
+
+
 def build_all(force: bool = False) -> None:
     build_library(force)
     build_host_demo(force)
+    build_stream_sweep(force)

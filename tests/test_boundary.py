@@ -129,6 +129,10 @@ def test_host_demo_builds(lib_built):
     assert exe and os.path.exists(exe)
     r = subprocess.run([exe, "--help"], capture_output=True, text=True)
     assert r.returncode == 0 and "driver threads" in r.stdout
+    exe = build.build_stream_sweep()
+    assert exe and os.path.exists(exe)
+    r = subprocess.run([exe, "--help"], capture_output=True, text=True)
+    assert r.returncode == 0 and "open loop" in r.stdout
 
 
 # ---------------------------------------------------------------- N > 1, one process per GPU (gloo on CPU)
