@@ -16,6 +16,8 @@
 #include "sort.cuh"
 #include "wire.hpp"
 
+#include <sched.h>
+
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -453,6 +455,51 @@ int32_t load_model_on_device(ctr_engine* e, int di, const HostWeights& hw) {
     return CTR_OK;
 }
 
+// ------------------------------------------------------------------ host locality
+// The CPUs on the socket a GPU hangs off (sysfs local_cpulist of its PCIe function), intersected with
+// what this process may run on.  Worker threads run there and the pinned staging buffers are allocated
+// from there (first touch), so H2D traffic does not cross the inter-socket link.  CTR_NO_CPU_BIND=1
+// turns it off; any failure just leaves the default placement.
+bool gpu_local_cpus(int dev, cpu_set_t* out) {
+    static const bool off = getenv("CTR_NO_CPU_BIND") != nullptr;
+    if (off) return false;
+    char bdf[32] = {0};
+    if (cudaDeviceGetPCIBusId(bdf, sizeof(bdf), dev) != cudaSuccess) { cudaGetLastError(); return false; }
+    for (char* c = bdf; *c; ++c) *c = (char)tolower(*c);
+    const std::string path = std::string("/sys/bus/pci/devices/") + bdf + "/local_cpulist";
+    FILE* f = fopen(path.c_str(), "r");
+    if (!f) return false;
+    char buf[1024] = {0};
+    const bool ok = fgets(buf, sizeof(buf), f) != nullptr;
+    fclose(f);
+    if (!ok) return false;
+    cpu_set_t allowed, local;
+    CPU_ZERO(&local);
+    if (sched_getaffinity(0, sizeof(allowed), &allowed) != 0) return false;
+    for (char* tok = strtok(buf, ",\n"); tok; tok = strtok(nullptr, ",\n")) {   // "0-31,64-95"
+        int a = 0, b = 0;
+        const int n = sscanf(tok, "%d-%d", &a, &b);
+        if (n < 1) continue;
+        if (n == 1) b = a;
+        for (int c = a; c <= b && c < CPU_SETSIZE; ++c) if (c >= 0 && CPU_ISSET(c, &allowed)) CPU_SET(c, &local);
+    }
+    if (CPU_COUNT(&local) == 0) return false;
+    *out = local;
+    return true;
+}
+
+// Runs the calling thread on the GPU-local CPUs for the lifetime of this object.
+struct ScopedGpuLocality {
+    cpu_set_t saved;
+    bool active = false;
+    explicit ScopedGpuLocality(int dev) {
+        cpu_set_t local;
+        if (gpu_local_cpus(dev, &local) && sched_getaffinity(0, sizeof(saved), &saved) == 0)
+            active = sched_setaffinity(0, sizeof(local), &local) == 0;
+    }
+    ~ScopedGpuLocality() { if (active) sched_setaffinity(0, sizeof(saved), &saved); }
+};
+
 // ------------------------------------------------------------------ slots
 void free_slot(Slot& s) {
     cudaSetDevice(s.dev);
@@ -792,6 +839,8 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
 
 void worker_main(ctr_engine* e, DeviceCtx* dc, Slot* s) {
     cudaSetDevice(s->dev);
+    cpu_set_t local;
+    if (gpu_local_cpus(s->dev, &local)) sched_setaffinity(0, sizeof(local), &local);   // stay next to the GPU
     for (;;) {
         Task t;
         {
@@ -934,6 +983,7 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
     for (int i = 0; i < e->cfg.n_devices; ++i) {
         DeviceCtx& dc = *e->devs[i];
         const int dev = e->cfg.device_ids[i];
+        ScopedGpuLocality near_gpu(dev);                       // pinned staging of this GPU is allocated on its socket
         for (int w = 0; w < e->cfg.workers_per_device; ++w) {
             std::unique_ptr<Slot> s(new Slot());
             if ((rc = init_slot_common(*s, dev, nullptr)) != CTR_OK) return rc;
@@ -1161,6 +1211,8 @@ int32_t ctr_alloc_pinned(ctr_engine* e, int64_t bytes, void** out) {
     if (!e || !out || bytes <= 0) return fail(CTR_ERR_INVALID, "ctr_alloc_pinned: bad argument");
     void* p = nullptr;
     CUDA_TRY(cudaSetDevice(e->cfg.device_ids[0]));
+    // a single-GPU engine knows which GPU will read the buffer: allocate it on that GPU's socket
+    std::unique_ptr<ScopedGpuLocality> near_gpu(e->cfg.n_devices == 1 ? new ScopedGpuLocality(e->cfg.device_ids[0]) : nullptr);
     CUDA_TRY(cudaHostAlloc(&p, (size_t)bytes, cudaHostAllocPortable));
     std::lock_guard<std::mutex> lk(e->pin_mu);
     e->pinned[(uintptr_t)p] = (size_t)bytes;

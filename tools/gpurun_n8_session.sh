@@ -1,0 +1,18 @@
+# One 8-GPU session: topology, multi-GPU parity tests, torchrun bench at N=8 (with and without the CPU binding),
+# request stream sweep at G = 1, 2, 4, 8.   gpurun --gpus 8 -- 'bash tools/gpurun_n8_session.sh'
+nvidia-smi --query-gpu=index,name --format=csv,noheader | head -8
+lscpu | grep -i "numa\|socket\|^CPU(s)" | head -8
+for d in /sys/bus/pci/devices/*; do if [ -e $d/local_cpulist ] && grep -q 0x10de $d/vendor 2>/dev/null; then echo "$(basename $d) $(cat $d/local_cpulist) numa $(cat $d/numa_node)"; fi; done | head -12
+timeout 600 python -m pytest tests/test_gpu_multi.py -q -m gpu -x --timeout 300 2>&1 | tail -4
+N=8
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29533 bench.py --gpus $N --steps 50 --warmup 5 > gpurun_out/r01_e_bench_n$N.json 2> gpurun_out/bench_n$N.err; tail -c 1200 gpurun_out/r01_e_bench_n$N.json; tail -3 gpurun_out/bench_n$N.err
+CTR_NO_CPU_BIND=1 timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29535 bench.py --gpus $N --steps 50 --warmup 5 --no-cpu-baseline > gpurun_out/r01_e_bench_n${N}_nobind.json 2>/dev/null; python - <<'PY'
+import json
+for f in ("gpurun_out/r01_e_bench_n8.json", "gpurun_out/r01_e_bench_n8_nobind.json"):
+    try:
+        d = json.loads([l for l in open(f) if l.startswith("{")][-1])
+        print(f, "value %.0fM e2e %.0fM shared %.0fM" % (d["value"] / 1e6, d["e2e"]["value"] / 1e6, d["e2e"]["shared_context"]["value"] / 1e6), d.get("latency"))
+    except Exception as ex:
+        print(f, "unreadable", ex)
+PY
+bash tools/gpurun_sweep.sh "1 2 4 8"
