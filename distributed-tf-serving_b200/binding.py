@@ -30,7 +30,7 @@ EXPORTS = ["ctr_engine_create", "ctr_engine_destroy", "ctr_engine_load_weights",
 class CtrConfig(C.Structure):
     _fields_ = [("struct_size", C.c_int32), ("n_devices", C.c_int32), ("device_ids", C.c_int32 * CTR_MAX_DEVICES),
                 ("max_candidates", C.c_int32), ("workers_per_device", C.c_int32), ("shard_mode", C.c_int32),
-                ("reserved", C.c_int32 * 8)]
+                ("min_shard_candidates", C.c_int32), ("reserved", C.c_int32 * 7)]
 
 
 class CtrModelInfo(C.Structure):
@@ -153,7 +153,7 @@ class Engine:
     "channel" per GPU."""
 
     def __init__(self, device_ids=(0,), max_candidates: int = 16384, workers_per_device: int = 0,
-                 shard_mode: int = TABLES_REPLICATED):
+                 shard_mode: int = TABLES_REPLICATED, min_shard_candidates: int = 0):
         self.lib = load_library()
         cfg = CtrConfig()
         cfg.struct_size = C.sizeof(CtrConfig)
@@ -163,6 +163,7 @@ class Engine:
         cfg.max_candidates = max_candidates
         cfg.workers_per_device = workers_per_device
         cfg.shard_mode = shard_mode
+        cfg.min_shard_candidates = min_shard_candidates       # 0: engine default; 1: always cut over all GPUs (DC:148)
         h = C.c_void_p()
         _check(self.lib.ctr_engine_create(C.byref(cfg), C.byref(h)))
         self.handle = h.value

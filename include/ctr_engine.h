@@ -65,7 +65,10 @@ typedef struct ctr_config {
     int32_t max_candidates;       /* capacity of ONE request (candidateNum, DC:29) */
     int32_t workers_per_device;   /* host threads (each with its own stream) per device; 0 = default 2 */
     int32_t shard_mode;           /* ctr_shard_mode */
-    int32_t reserved[8];
+    int32_t min_shard_candidates; /* a request is spread over floor(n / this) GPUs, at most n_devices, at least 1
+                                   * (the starting GPU rotates); 0 = default 1024; 1 = always cut n_devices ways
+                                   * as DC:148 does.  Scores do not depend on it. */
+    int32_t reserved[7];
 } ctr_config;
 
 typedef struct ctr_engine ctr_engine;

@@ -36,10 +36,17 @@ def test_candidate_sharding_equals_single_gpu(binding, weight_file, kind_name, n
         e1.load_weights(path)
         one = e1.predict(ids, wts).copy()
     for g in sorted({2, G}):
-        with binding.Engine(device_ids=tuple(range(g)), max_candidates=16384) as eg:
+        # min_shard_candidates=1: cut over all g GPUs whatever the size, as the reference does (DC:148)
+        with binding.Engine(device_ids=tuple(range(g)), max_candidates=16384, min_shard_candidates=1) as eg:
             eg.load_weights(path)
             many = eg.predict(ids, wts).copy()
         assert np.array_equal(many, one), "%d GPUs: max |d| = %g" % (g, np.abs(many - one).max())
+        # engine default: shards of >= 1024 candidates, first GPU rotating -- consecutive small requests
+        # land on different GPUs and every one of them must give the same bits
+        with binding.Engine(device_ids=tuple(range(g)), max_candidates=16384) as eg:
+            eg.load_weights(path)
+            for rep in range(g + 1):
+                assert np.array_equal(eg.predict(ids, wts), one), "%d GPUs, default sharding, request %d" % (g, rep)
     tol = 1e-5 if kind == om.LR else 2e-3
     assert np.abs(one - om.forward(w, ids, wts, "fp64")).max() <= tol
 
@@ -60,7 +67,8 @@ def test_row_sharded_tables_equal_replicated(binding, weight_file, hashed):
         with binding.Engine(device_ids=(0,), max_candidates=4096) as e1:
             e1.load_weights(path)
             one = e1.predict(ids, wts).copy()
-        with binding.Engine(device_ids=tuple(range(G)), max_candidates=4096, shard_mode=binding.TABLES_ROW_SHARDED) as es:
+        with binding.Engine(device_ids=tuple(range(G)), max_candidates=4096, shard_mode=binding.TABLES_ROW_SHARDED,
+                            min_shard_candidates=1) as es:
             info = es.load_weights(path)
             sharded = es.predict(ids, wts).copy()
             rows = np.arange(0, min(w.spec.num_rows, 4096))
