@@ -16,3 +16,12 @@ for f in ("gpurun_out/r01_e_bench_n8.json", "gpurun_out/r01_e_bench_n8_nobind.js
         print(f, "unreadable", ex)
 PY
 bash tools/gpurun_sweep.sh "1 2 4 8"
+# config 3: DeepFM, 100 000 candidates per request cut over the GPUs of one engine (through the C ABI, pinned host buffers)
+python - <<'PY'
+import dtfs_b200, bench
+bench.write_model("/tmp/deepfm_sweep.ctrw", 1 << 22, model="deepfm")
+PY
+for g in 1 8; do echo "== config 3 (DeepFM, 100k candidates/request) on $g GPU(s)"; timeout 600 ./distributed-tf-serving_b200/stream_sweep_host --lib distributed-tf-serving_b200/libctr_b200.so --weights /tmp/deepfm_sweep.ctrw --devices $g --min 100000 --max 100000 --requests 3000 --out gpurun_out/r01_config3_g$g.md; done
+# config 4: DCN-v2, ids hashed into ONE 2^30-row fp32 table (137 GB), rows striped over the 8 GPUs, remote rows over NVLink
+echo "== config 4, 2^27 rows (replicated vs row-sharded)"; timeout 900 python tools/bench_row_sharded.py --log2-rows 27 2>&1 | tail -1
+echo "== config 4, 2^30 rows (row-sharded only)"; timeout 900 python tools/bench_row_sharded.py --log2-rows 30 --skip-replicated 2>&1 | tail -1
