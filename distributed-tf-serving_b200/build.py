@@ -10,7 +10,9 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libctr_b200.so")
 HOST_DEMO = os.path.join(HERE, "dcn_client_host")
 STREAM_SWEEP = os.path.join(HERE, "stream_sweep_host")
-SOURCES = ["engine.cu", "common.cuh", "gather.cuh", "tower.cuh", "sort.cuh", "wire.hpp", os.path.join("..", "..", "include", "ctr_engine.h")]
+SOURCES = ["engine.cu", "engine_base.cuh", "weight_file.cuh", "engine_state.cuh", "device_setup.cuh", "device_path.cuh", "workers.cuh",
+           "debug_hooks.cuh", "static_scratch.cuh", "common.cuh", "gather.cuh", "tower.cuh", "sort.cuh", "wire.hpp",
+           os.path.join("..", "..", "include", "ctr_engine.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-Wall,-pthread", "-shared"]

@@ -1,0 +1,141 @@
+// device_path.cuh -- the kernels of one chunk of candidates on a slot's stream: gather, then the chains.
+#pragma once
+namespace {
+// ------------------------------------------------------------------ the device path for one chunk
+template <int TD, bool H, bool E, bool L, bool FM, bool S>
+void launch_gather_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    gather_pool_kernel<TD, H, E, L, FM, S><<<grid, kGatherThreads, smem, st>>>(gp);
+}
+
+template <int TD, bool H, bool S>
+void launch_gather_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    switch (kind) {
+        case CTR_MODEL_LR: launch_gather_t<TD, H, false, true, false, S>(gp, grid, smem, st); break;
+        case CTR_MODEL_WIDE_DEEP: launch_gather_t<TD, H, true, true, false, S>(gp, grid, smem, st); break;
+        case CTR_MODEL_DEEPFM: launch_gather_t<TD, H, true, true, true, S>(gp, grid, smem, st); break;
+        default: launch_gather_t<TD, H, true, false, false, S>(gp, grid, smem, st); break;
+    }
+}
+
+void launch_gather(const ModelDesc& m, bool sharded, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    const bool hashed = m.id_mode == CTR_ID_HASHED;
+    if (m.table_dtype == CTR_TABLE_FP32) {
+        if (sharded) { if (hashed) launch_gather_kind<0, true, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, false, true>(m.kind, gp, grid, smem, st); }
+        else { if (hashed) launch_gather_kind<0, true, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, false, false>(m.kind, gp, grid, smem, st); }
+    } else {
+        if (sharded) { if (hashed) launch_gather_kind<1, true, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, false, true>(m.kind, gp, grid, smem, st); }
+        else { if (hashed) launch_gather_kind<1, true, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, false, false>(m.kind, gp, grid, smem, st); }
+    }
+}
+
+// One chain on `st`: persistent CTA pairs, at most one pair per TPC and per scratch slice.
+int32_t launch_chain(const Chain& c, const Slot& s, int n, float* d_scores, int num_sms, cudaStream_t st, long long* prof = nullptr) {
+    ChainParams p = c.params;
+    p.M = n;
+    p.prof = prof;
+    if (!p.extra_out) p.scores = d_scores;
+    const int tiles = (n + 2 * kBM - 1) / (2 * kBM);
+    const int pairs = std::max(1, std::min(std::min(tiles, num_sms / 2), s.scratch_rows / (2 * kBM)));
+    tower_chain_kernel<256><<<2 * pairs, kGemmThreads, ChainCfg<256>::kSmemBytes, st>>>(c.maps, p);
+    CUDA_TRY(cudaGetLastError());
+    return CTR_OK;
+}
+
+// Records a CUDA event on the launching stream in front of a stage (stage -2 = end of chunk).
+void mark(ctr_engine* e, Slot& s, int stage) {
+    if (!e->timing || !s.time_this || !s.tev || s.sets_recorded >= Slot::kTimeSets || s.cur_mark >= Slot::kTimeMarks) return;
+    s.mark_stage[s.cur_mark] = stage;
+    cudaEventRecord(s.tev[s.sets_recorded][s.cur_mark++], s.stream);
+    if (stage == -2) { s.n_marks = s.cur_mark; s.cur_mark = 0; ++s.sets_recorded; s.time_this = false; }
+}
+
+// Scores rows [0, n) of (d_ids, d_wts) into d_scores on s.stream; n <= s.x_rows for tower models.
+int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int n, float* d_scores) {
+    const ModelDesc& m = e->m;
+    DeviceModel& dm = dc.model;
+    cudaStream_t st = s.stream;
+    const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1;
+
+    GatherParams gp;
+    memset(&gp, 0, sizeof(gp));
+    gp.ids = d_ids; gp.wts = d_wts; gp.n = n; gp.F = m.F;
+    gp.bulk_ok = ((reinterpret_cast<uintptr_t>(d_ids) | reinterpret_cast<uintptr_t>(d_wts)) & 15) == 0;
+    gp.table = dm.table; gp.num_rows = (uint64_t)m.V; gp.b0 = dm.b0;
+    gp.error_flag = s.d_err;
+    gp.n_shards = sharded ? e->cfg.n_devices : 1;
+    for (int g = 0; g < CTR_MAX_DEVICES; ++g) gp.shard_base[g] = e->shard_base[g];
+    if (m.kind == CTR_MODEL_LR) { gp.scores = d_scores; }
+    else { gp.X = s.buf[0]; gp.ldx = s.ld[0]; gp.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide; }
+    const int n_tiles = (n + kGatherTile - 1) / kGatherTile;
+    static const int gather_ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : CTR_GATHER_MIN_CTAS; }();
+    const int ggrid = std::max(1, std::min(n_tiles, dm.num_sms * gather_ctas_per_sm));
+    const size_t gsmem = (size_t)2 * kGatherTile * m.F * 12;
+    mark(e, s, 0);
+    launch_gather(m, sharded, gp, ggrid, gsmem, st);
+    CUDA_TRY(cudaGetLastError());
+    e->launches.fetch_add(1, std::memory_order_relaxed);
+    int li = 0;
+    static const bool chain_prof = getenv("CTR_CHAIN_PROF") != nullptr;      // bring-up: in-kernel cycle counters to stderr
+    for (const Chain& c : s.chains) {
+        mark(e, s, ++li);
+        long long* d_prof = nullptr;
+        if (chain_prof) {
+            CUDA_TRY(cudaMalloc(&d_prof, (size_t)dm.num_sms * 8 * sizeof(long long)));
+            CUDA_TRY(cudaMemsetAsync(d_prof, 0, (size_t)dm.num_sms * 8 * sizeof(long long), st));
+        }
+        int32_t rc = launch_chain(c, s, n, d_scores, dm.num_sms, st, d_prof);
+        if (rc != CTR_OK) return rc;
+        e->launches.fetch_add(1, std::memory_order_relaxed);
+        if (chain_prof) {
+            std::vector<long long> h((size_t)dm.num_sms * 8);
+            CUDA_TRY(cudaMemcpyAsync(h.data(), d_prof, h.size() * sizeof(long long), cudaMemcpyDeviceToHost, st));
+            CUDA_TRY(cudaStreamSynchronize(st));
+            const char* names[8] = {"producer wait empty", "mma wait acc_empty", "mma wait full", "mma issue+commit", "mma loop total",
+                                    "epi wait acc_full", "epi body", "producer wait layer"};
+            fprintf(stderr, "[chain prof] chain %d: %d layers, BN=%d, n=%d (cycles, mean over leader CTAs)\n", li, c.n_layers, c.BN, n);
+            for (int i = 0; i < 8; ++i) {
+                double mean = 0; int cnt = 0;
+                for (int cta = 0; cta < dm.num_sms; cta += 2) { mean += (double)h[cta * 8 + i]; ++cnt; }
+                fprintf(stderr, "  %-22s %12.0f\n", names[i], mean / cnt);
+            }
+            double cyc = 0, ns = 0;
+            for (int cta = 0; cta + 1 < dm.num_sms; cta += 2) { cyc += (double)h[cta * 8 + 4]; ns += (double)h[(cta + 1) * 8 + 4]; }
+            if (ns > 0) fprintf(stderr, "  %-22s %12.0f MHz (cycles / globaltimer over the MMA loop)\n", "effective SM clock", cyc / ns * 1000.0);
+            cudaFree(d_prof);
+        }
+    }
+    mark(e, s, -2);
+    return CTR_OK;
+}
+
+// Scores n candidates (device pointers) on slot s, chunked so activations stay in their buffers.
+int32_t score_on_slot(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int64_t n, float* d_scores) {
+    const int F = e->m.F;
+    const int64_t step = e->m.kind == CTR_MODEL_LR ? (int64_t)1 << 30 : s.x_rows;
+    for (int64_t c0 = 0; c0 < n; c0 += step) {
+        const int cnt = (int)std::min<int64_t>(step, n - c0);
+        s.time_this = false;                   // stage timing is for ctr_score_device calls
+        int32_t rc = score_chunk(e, dc, s, d_ids + c0 * F, d_wts + c0 * F, cnt, d_scores + c0);
+        if (rc != CTR_OK) return rc;
+    }
+    return CTR_OK;
+}
+
+// Mean device time of `stage` over the recorded sets (caller has synchronised the device).
+double mean_stage_ms(Slot& s, int stage) {
+    if (!s.tev || s.sets_recorded == 0 || s.n_marks < 2) return -1.0;
+    double sum = 0.0; int cnt = 0;
+    for (int set = 0; set < s.sets_recorded; ++set) {
+        double acc = 0.0; bool any = false;
+        for (int i = 0; i + 1 < s.n_marks; ++i) {
+            if (stage != -1 && s.mark_stage[i] != stage) continue;
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, s.tev[set][i], s.tev[set][i + 1]) != cudaSuccess) { (void)cudaGetLastError(); any = false; break; }
+            acc += ms; any = true;
+        }
+        if (any) { sum += acc; ++cnt; }
+    }
+    return cnt ? sum / cnt : -1.0;
+}
+
+}  // namespace

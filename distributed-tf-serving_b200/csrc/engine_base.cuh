@@ -1,0 +1,73 @@
+// engine_base.cuh -- error reporting, small helpers and the tensor-map encoders of the host runtime
+// (included by engine.cu only: one translation unit, everything here has internal linkage).
+#pragma once
+namespace {
+
+using namespace ctr;
+
+thread_local std::string g_last_error;
+
+int32_t fail(int32_t code, const std::string& msg) {
+    g_last_error = msg;
+    return code;
+}
+
+#define CUDA_TRY(expr)                                                                                   \
+    do {                                                                                                 \
+        cudaError_t _e = (expr);                                                                         \
+        if (_e != cudaSuccess) {                                                                         \
+            (void)cudaGetLastError();                                                                    \
+            return fail(CTR_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));               \
+        }                                                                                                \
+    } while (0)
+
+inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// ------------------------------------------------------------------ driver entry point for tensor maps
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn get_encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// half matrix [rows, cols] with leading dimension ld (elements), box {64, box_rows}, 128-byte swizzle
+int32_t make_map_f16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {ld * sizeof(__half)};
+    cuuint32_t box[2] = {(cuuint32_t)kBK, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    return CTR_OK;
+}
+
+// 3-D map over a tile-major activation buffer of `ld` columns (tower.cuh): per 128-row tile the K blocks
+// are contiguous 16 KB runs, described as 32 lines of 512 B; no swizzle, so a box lands in shared memory
+// byte for byte.  Coordinates: (0, 32 * k_block, tile).
+int32_t make_map_tile_major(CUtensorMap* map, const void* base, uint64_t ld, uint64_t n_tiles) {
+    EncodeTiledFn fn = get_encode_fn();
+    if (!fn) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[3] = {256, ld / 2, n_tiles};
+    cuuint64_t strides[2] = {512, (cuuint64_t)kBM * ld * sizeof(__half)};
+    cuuint32_t box[3] = {256, 32, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(CTR_ERR_CUDA, "cuTensorMapEncodeTiled (tile-major) failed with CUresult " + std::to_string((int)r));
+    return CTR_OK;
+}
+
+}  // namespace

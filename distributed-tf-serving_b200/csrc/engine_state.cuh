@@ -1,0 +1,135 @@
+// engine_state.cuh -- what the engine holds: the model on each device, slots (a stream with its private
+// activation buffers), per-device worker queues, tickets, and struct ctr_engine itself.
+#pragma once
+namespace {
+// ------------------------------------------------------------------ per-device model state
+struct GemmLayer {
+    int N = 0, Npad = 0, Kpad = 0;
+    __half* W = nullptr;      // [Npad, Kpad]
+    float* bias = nullptr;    // [Npad]
+};
+
+struct DeviceModel {
+    int dev = -1;
+    int num_sms = 148;
+    uint8_t* table = nullptr;          // packed rows (local shard when row-sharded)
+    uint64_t table_rows_local = 0;
+    size_t table_bytes = 0;
+    std::vector<GemmLayer> mlp, cross;
+    float* w_out_h = nullptr;          // [Npad of last hidden] head weights for the hidden part
+    float* w_out_x = nullptr;          // [d_pad] head weights for x_L (DCN-v2)
+    float b0 = 0.f, b_out = 0.f;
+    bool loaded = false;
+};
+
+// One launch of tower_chain_kernel: a sequence of layers, each feeding the next.
+struct Chain {
+    int BN = 256;
+    int n_layers = 0;
+    ChainMaps maps;
+    ChainParams params;       // template: M / score pointer are filled per launch
+};
+
+// One stream with its private activation buffers ("slot"): everything a shard needs on the device.
+struct Slot {
+    int dev = -1;
+    cudaStream_t stream = nullptr;
+    bool owns_stream = true;
+    int64_t cap = 0;           // candidate capacity of the id/weight/score buffers
+    int x_rows = 0;            // candidates per launch: rows of X / wide / extra (multiple of 256)
+    int scratch_rows = 0;      // rows of the per-pair scratch (resident CTA pairs x 256)
+    int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;
+    int64_t* d_cids = nullptr; float* d_cwts = nullptr;     // compact lists of a shared-context request (host slots)
+    float* d_wide = nullptr; float* d_extra = nullptr; int32_t* d_err = nullptr;
+    __half* buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int ld[6] = {0, 0, 0, 0, 0, 0};
+    std::vector<Chain> chains;
+    // pinned staging for pageable callers
+    int64_t* h_ids = nullptr; float* h_wts = nullptr; float* h_scores = nullptr; int32_t* h_err = nullptr;
+    // stage timing: a ring of event sets, one set per timed call (first chunk of the call only)
+    static constexpr int kTimeSets = 32, kTimeMarks = 12;
+    cudaEvent_t (*tev)[kTimeMarks] = nullptr;      // [kTimeSets][kTimeMarks], created when timing is switched on
+    int mark_stage[kTimeMarks]; int n_marks = 0;   // stage id of mark i (same sequence every call)
+    int cur_mark = 0; int sets_recorded = 0; bool time_this = false;
+    cudaEvent_t join_ev = nullptr;
+};
+
+struct Request {
+    std::atomic<int> pending{0};
+    std::atomic<int> status{CTR_OK};
+    std::string error;
+    std::mutex m;
+    std::condition_variable cv;
+    bool done = false;
+    ctr_callback cb = nullptr;
+    void* user = nullptr;
+    ctr_ticket ticket = 0;
+};
+
+struct Task {
+    std::shared_ptr<Request> req;
+    const int64_t* ids; const float* wts; int64_t n; float* scores;
+    // shared-context request: the first n_ctx fields of every candidate come from one shared list and
+    // ids / wts hold only the remaining F - n_ctx fields per candidate
+    const int64_t* ctx_ids = nullptr; const float* ctx_wts = nullptr; int32_t n_ctx = 0;
+    bool stop = false;
+};
+
+struct DeviceCtx {
+    DeviceModel model;
+    std::vector<std::unique_ptr<Slot>> worker_slots;
+    std::vector<std::unique_ptr<Slot>> dev_slots;     // for ctr_score_device
+    std::mutex dev_mu;                                // serialises ctr_score_device enqueues per device
+    cudaStream_t main_stream = nullptr;
+    cudaEvent_t fork_ev = nullptr;
+    // device sort scratch (ctr_predict_sorted), allocated on first use
+    std::mutex sort_mu;
+    int64_t sort_cap = 0;
+    float* srt_scores = nullptr; float* srt_sorted = nullptr; uint32_t* srt_keys[2] = {nullptr, nullptr};
+    int32_t* srt_idx[2] = {nullptr, nullptr}; uint32_t* srt_counts = nullptr;
+    std::deque<Task> queue;
+    std::mutex q_mu;
+    std::condition_variable q_cv;
+    std::vector<std::thread> threads;
+};
+
+}  // namespace
+
+struct ctr_engine {
+    ctr_config cfg;
+    ModelDesc m;
+    bool loaded = false;
+    bool timing = false;
+    int chunk_rows = 0;          // 0 = num_sms * 128
+    std::vector<std::unique_ptr<DeviceCtx>> devs;
+    std::mutex t_mu;
+    std::unordered_map<ctr_ticket, std::shared_ptr<Request>> tickets;
+    std::atomic<int64_t> next_ticket{1};
+    std::atomic<int64_t> launches{0};
+    std::mutex pin_mu;
+    std::map<uintptr_t, size_t> pinned;     // base -> bytes (buffers from ctr_alloc_pinned)
+    std::atomic<unsigned> next_first_device{0};   // rotation of the first GPU of requests that use fewer than all
+    std::atomic<bool> shutting_down{false};
+    uint8_t* shard_base[CTR_MAX_DEVICES] = {nullptr};   // row-sharded tables: every device's shard
+};
+
+namespace {
+
+// DC:46-55 applied to candidates
+void split_bounds(int64_t n, int parts, int64_t* b, int64_t* e) {
+    const int64_t range = n / parts;
+    for (int i = 0; i < parts - 1; ++i) { b[i] = i * range; e[i] = (i + 1) * range; }
+    b[parts - 1] = (int64_t)(parts - 1) * range;
+    e[parts - 1] = n;
+}
+
+bool is_pinned(ctr_engine* e, const void* p, size_t bytes) {
+    std::lock_guard<std::mutex> lk(e->pin_mu);
+    if (e->pinned.empty()) return false;
+    auto it = e->pinned.upper_bound((uintptr_t)p);
+    if (it == e->pinned.begin()) return false;
+    --it;
+    return (uintptr_t)p >= it->first && (uintptr_t)p + bytes <= it->first + it->second;
+}
+
+}  // namespace

@@ -1,0 +1,122 @@
+// workers.cuh -- the host side of a request: shard tasks, worker threads (the reference's threadPool,
+// DC:42), staging + copies + kernels per shard (sendRequest, DC:91-115), completion and tickets.
+#pragma once
+namespace {
+// ------------------------------------------------------------------ request completion
+void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t status, const std::string& err) {
+    if (status != CTR_OK) {
+        int expected = CTR_OK;
+        if (r->status.compare_exchange_strong(expected, status)) {
+            std::lock_guard<std::mutex> lk(r->m);
+            r->error = err;
+        }
+    }
+    if (r->pending.fetch_sub(1) == 1) {
+        {
+            std::lock_guard<std::mutex> lk(r->m);
+            r->done = true;
+        }
+        r->cv.notify_all();
+        if (r->cb) r->cb(r->user, r->ticket, r->status.load());
+    }
+}
+
+// sendRequest (DC:91-115) for one shard: stage -> H2D -> kernels -> D2H -> hand back.
+void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
+    const ModelDesc& m = e->m;
+    auto body = [&]() -> int32_t {
+        CUDA_TRY(cudaSetDevice(s.dev));
+        const int Fk = m.F - t.n_ctx;                          // per-candidate fields actually shipped
+        const size_t ib = (size_t)t.n * Fk * sizeof(int64_t), wb = (size_t)t.n * Fk * sizeof(float), sb = (size_t)t.n * sizeof(float);
+        // The feature packer: caller buffers that came from ctr_alloc_pinned are DMA'd in place;
+        // pageable ones (a Java heap array, a numpy array) are packed into this slot's pinned slab.
+        const int64_t* src_ids = t.ids;
+        const float* src_wts = t.wts;
+        if (!is_pinned(e, t.ids, ib)) { memcpy(s.h_ids, t.ids, ib); src_ids = s.h_ids; }
+        if (!is_pinned(e, t.wts, wb)) { memcpy(s.h_wts, t.wts, wb); src_wts = s.h_wts; }
+        const bool out_pinned = is_pinned(e, t.scores, sb);
+        float* dst_scores = out_pinned ? t.scores : s.h_scores;
+        if (t.n_ctx == 0) {
+            CUDA_TRY(cudaMemcpyAsync(s.d_ids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(s.d_wts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
+        } else {
+            // shared context: ship the per-candidate fields once and the context list once, rebuild the
+            // reference layout [n, F] on the device (HBM bandwidth is cheap, the host link is not)
+            CUDA_TRY(cudaMemcpyAsync(s.d_cids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(s.d_cwts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
+            int64_t* d_ctx_ids = s.d_cids + (size_t)s.cap * m.F;
+            float* d_ctx_wts = s.d_cwts + (size_t)s.cap * m.F;
+            CUDA_TRY(cudaMemcpyAsync(d_ctx_ids, t.ctx_ids, (size_t)t.n_ctx * sizeof(int64_t), cudaMemcpyHostToDevice, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(d_ctx_wts, t.ctx_wts, (size_t)t.n_ctx * sizeof(float), cudaMemcpyHostToDevice, s.stream));
+            const int64_t total = t.n * m.F;
+            expand_context_kernel<<<(int)std::min<int64_t>((total + 255) / 256, dc.model.num_sms * 16), 256, 0, s.stream>>>(
+                d_ctx_ids, d_ctx_wts, t.n_ctx, s.d_cids, s.d_cwts, t.n, m.F, s.d_ids, s.d_wts);
+            CUDA_TRY(cudaGetLastError());
+            e->launches.fetch_add(1, std::memory_order_relaxed);
+        }
+        int32_t rc = score_on_slot(e, dc, s, s.d_ids, s.d_wts, t.n, s.d_scores);
+        if (rc != CTR_OK) return rc;
+        CUDA_TRY(cudaMemcpyAsync(dst_scores, s.d_scores, sb, cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(s.h_err, s.d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        if (*s.h_err) {
+            CUDA_TRY(cudaMemsetAsync(s.d_err, 0, sizeof(int32_t), s.stream));
+            return fail(CTR_ERR_INVALID, "feature id out of range for a direct-indexed table");
+        }
+        if (!out_pinned) memcpy(t.scores, s.h_scores, sb);
+        return CTR_OK;
+    };
+    int32_t rc = body();
+    complete_shard(e, t.req, rc, rc == CTR_OK ? std::string() : g_last_error);
+}
+
+void worker_main(ctr_engine* e, DeviceCtx* dc, Slot* s) {
+    cudaSetDevice(s->dev);
+    cpu_set_t local;
+    if (gpu_local_cpus(s->dev, &local)) sched_setaffinity(0, sizeof(local), &local);   // stay next to the GPU
+    for (;;) {
+        Task t;
+        {
+            std::unique_lock<std::mutex> lk(dc->q_mu);
+            dc->q_cv.wait(lk, [&] { return !dc->queue.empty(); });
+            t = dc->queue.front();
+            if (t.stop) return;                 // leave the stop marker for the other workers
+            dc->queue.pop_front();
+        }
+        run_task(e, *dc, *s, t);
+    }
+}
+
+void stop_workers(ctr_engine* e) {
+    for (auto& dcp : e->devs) {
+        DeviceCtx& dc = *dcp;
+        if (dc.threads.empty()) continue;
+        {
+            std::lock_guard<std::mutex> lk(dc.q_mu);
+            Task t; t.stop = true; t.ids = nullptr; t.wts = nullptr; t.n = 0; t.scores = nullptr;
+            dc.queue.push_back(t);
+        }
+        dc.q_cv.notify_all();
+        for (auto& th : dc.threads) th.join();
+        dc.threads.clear();
+        dc.queue.clear();
+    }
+}
+
+void free_device_state(ctr_engine* e) {
+    for (auto& dcp : e->devs) {
+        DeviceCtx& dc = *dcp;
+        for (auto& s : dc.worker_slots) free_slot(*s);
+        for (auto& s : dc.dev_slots) free_slot(*s);
+        dc.worker_slots.clear();
+        dc.dev_slots.clear();
+        if (dc.model.dev >= 0) free_model(dc.model);
+        if (dc.sort_cap) {
+            cudaFree(dc.srt_scores); cudaFree(dc.srt_sorted); cudaFree(dc.srt_counts);
+            for (int i = 0; i < 2; ++i) { cudaFree(dc.srt_keys[i]); cudaFree(dc.srt_idx[i]); }
+            dc.sort_cap = 0;
+        }
+    }
+}
+
+}  // namespace
