@@ -232,6 +232,7 @@ static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx
         {
             std::lock_guard<std::mutex> lk(dc.q_mu);
             dc.queue.push_back(t);
+            dc.queued.fetch_add(1, std::memory_order_release);
         }
         dc.q_cv.notify_one();
     }
@@ -258,6 +259,7 @@ int32_t ctr_wait(ctr_engine* e, ctr_ticket ticket, int32_t timeout_ms) {
         if (it == e->tickets.end()) return fail(CTR_ERR_STATE, "ctr_wait: unknown or already released ticket");
         r = it->second;
     }
+    if (timeout_ms != 0) poll_briefly([&] { return r->done_flag.load(std::memory_order_acquire); });
     {
         std::unique_lock<std::mutex> lk(r->m);
         if (timeout_ms < 0) r->cv.wait(lk, [&] { return r->done; });

@@ -61,6 +61,7 @@ struct Request {
     std::mutex m;
     std::condition_variable cv;
     bool done = false;
+    std::atomic<bool> done_flag{false};   // same as `done`, readable without the mutex (ctr_wait polls it briefly first)
     ctr_callback cb = nullptr;
     void* user = nullptr;
     ctr_ticket ticket = 0;
@@ -88,6 +89,7 @@ struct DeviceCtx {
     float* srt_scores = nullptr; float* srt_sorted = nullptr; uint32_t* srt_keys[2] = {nullptr, nullptr};
     int32_t* srt_idx[2] = {nullptr, nullptr}; uint32_t* srt_counts = nullptr;
     std::deque<Task> queue;
+    std::atomic<int> queued{0};                       // queue.size(), readable without q_mu (workers poll it briefly before sleeping)
     std::mutex q_mu;
     std::condition_variable q_cv;
     std::vector<std::thread> threads;

@@ -15,6 +15,7 @@ void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t st
         {
             std::lock_guard<std::mutex> lk(r->m);
             r->done = true;
+            r->done_flag.store(true, std::memory_order_release);
         }
         r->cv.notify_all();
         if (r->cb) r->cb(r->user, r->ticket, r->status.load());
@@ -76,12 +77,14 @@ void worker_main(ctr_engine* e, DeviceCtx* dc, Slot* s) {
     if (gpu_local_cpus(s->dev, &local)) sched_setaffinity(0, sizeof(local), &local);   // stay next to the GPU
     for (;;) {
         Task t;
+        poll_briefly([&] { return dc->queued.load(std::memory_order_acquire) > 0; });
         {
             std::unique_lock<std::mutex> lk(dc->q_mu);
             dc->q_cv.wait(lk, [&] { return !dc->queue.empty(); });
             t = dc->queue.front();
             if (t.stop) return;                 // leave the stop marker for the other workers
             dc->queue.pop_front();
+            dc->queued.fetch_sub(1, std::memory_order_relaxed);
         }
         run_task(e, *dc, *s, t);
     }
@@ -95,11 +98,13 @@ void stop_workers(ctr_engine* e) {
             std::lock_guard<std::mutex> lk(dc.q_mu);
             Task t; t.stop = true; t.ids = nullptr; t.wts = nullptr; t.n = 0; t.scores = nullptr;
             dc.queue.push_back(t);
+            dc.queued.fetch_add(1, std::memory_order_release);
         }
         dc.q_cv.notify_all();
         for (auto& th : dc.threads) th.join();
         dc.threads.clear();
         dc.queue.clear();
+        dc.queued.store(0);
     }
 }
 
