@@ -138,4 +138,32 @@ double mean_stage_ms(Slot& s, int stage) {
     return cnt ? sum / cnt : -1.0;
 }
 
+// ------------------------------------------------------------------ A6: the sort of processARequest (DC:195)
+// Sorts d_scores[0, n) on `st` (ascending, Float.compareTo order, ties by candidate index): the sorted scores
+// land in b.sorted, the candidate index of each in *d_order (one of b.idx).
+int32_t launch_sort(ctr_engine* e, const DeviceModel& dm, SortBufs& b, const float* d_scores, int n, cudaStream_t st, const int32_t** d_order) {
+    if (n <= kBlockSortMax) {                                   // one block, one launch
+        sort_block_kernel<<<1, kBlockSortThreads, 0, st>>>(d_scores, n, b.keys[0], b.idx[0], b.keys[1], b.idx[1], b.sorted);
+        CUDA_TRY(cudaGetLastError());
+        e->launches.fetch_add(1, std::memory_order_relaxed);
+        *d_order = b.idx[0];
+        return CTR_OK;
+    }
+    const int n_blocks = (n + kSortTile - 1) / kSortTile;
+    const int g1 = std::max(1, std::min((n + 255) / 256, dm.num_sms * 8));
+    sort_make_keys_kernel<<<g1, 256, 0, st>>>(d_scores, n, b.keys[0], b.idx[0]);
+    int cur = 0;
+    for (int pass = 0; pass < 4; ++pass) {
+        sort_hist_kernel<<<n_blocks, kSortThreads, 0, st>>>(b.keys[cur], n, pass * 8, b.counts);
+        sort_scan_kernel<<<1, 1024, 0, st>>>(b.counts, 256 * n_blocks);
+        sort_scatter_kernel<<<n_blocks, kSortThreads, 0, st>>>(b.keys[cur], b.idx[cur], n, pass * 8, b.counts, b.keys[cur ^ 1], b.idx[cur ^ 1]);
+        cur ^= 1;
+    }
+    sort_gather_scores_kernel<<<g1, 256, 0, st>>>(d_scores, b.idx[cur], n, b.sorted);
+    CUDA_TRY(cudaGetLastError());
+    e->launches.fetch_add(14, std::memory_order_relaxed);
+    *d_order = b.idx[cur];
+    return CTR_OK;
+}
+
 }  // namespace

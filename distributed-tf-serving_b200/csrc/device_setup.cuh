@@ -188,11 +188,32 @@ struct ScopedGpuLocality {
 };
 
 // ------------------------------------------------------------------ slots
+// buffers of the device sort (launch_sort, device_path.cuh)
+void free_sort_bufs(SortBufs& b) {
+    cudaFree(b.sorted); cudaFree(b.counts);
+    for (int i = 0; i < 2; ++i) { cudaFree(b.keys[i]); cudaFree(b.idx[i]); }
+    b = SortBufs();
+}
+
+int32_t alloc_sort_bufs(SortBufs& b, int64_t cap) {
+    if (b.cap >= cap) return CTR_OK;
+    free_sort_bufs(b);
+    CUDA_TRY(cudaMalloc(&b.sorted, cap * sizeof(float)));
+    for (int i = 0; i < 2; ++i) {
+        CUDA_TRY(cudaMalloc(&b.keys[i], cap * sizeof(uint32_t)));
+        CUDA_TRY(cudaMalloc(&b.idx[i], cap * sizeof(int32_t)));
+    }
+    CUDA_TRY(cudaMalloc(&b.counts, (size_t)256 * ((cap + kSortTile - 1) / kSortTile) * sizeof(uint32_t)));
+    b.cap = cap;
+    return CTR_OK;
+}
+
 void free_slot(Slot& s) {
     cudaSetDevice(s.dev);
     cudaFree(s.d_ids); cudaFree(s.d_wts); cudaFree(s.d_scores); cudaFree(s.d_cids); cudaFree(s.d_cwts); cudaFree(s.d_wide); cudaFree(s.d_extra); cudaFree(s.d_err);
     for (auto*& b : s.buf) { cudaFree(b); b = nullptr; }
-    cudaFreeHost(s.h_ids); cudaFreeHost(s.h_wts); cudaFreeHost(s.h_scores); cudaFreeHost(s.h_err);
+    cudaFreeHost(s.h_ids); cudaFreeHost(s.h_wts); cudaFreeHost(s.h_scores); cudaFreeHost(s.h_err); cudaFreeHost(s.h_order);
+    free_sort_bufs(s.srt);
     if (s.tev) {
         for (int i = 0; i < Slot::kTimeSets; ++i) for (int j = 0; j < Slot::kTimeMarks; ++j) cudaEventDestroy(s.tev[i][j]);
         delete[] s.tev;
@@ -285,6 +306,9 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
         CUDA_TRY(cudaMallocHost(&s.h_wts, (size_t)s.cap * m.F * sizeof(float)));
         CUDA_TRY(cudaMallocHost(&s.h_scores, (size_t)s.cap * sizeof(float)));
         CUDA_TRY(cudaMallocHost(&s.h_err, sizeof(int32_t)));
+        CUDA_TRY(cudaMallocHost(&s.h_order, (size_t)s.cap * sizeof(int32_t)));
+        int32_t src = alloc_sort_bufs(s.srt, s.cap);           // 24 B per candidate: ctr_predict_sorted never allocates on the request path
+        if (src != CTR_OK) return src;
     }
     if (m.kind == CTR_MODEL_LR) return CTR_OK;
 

@@ -183,7 +183,7 @@ int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out) {
 
 static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx_ids, const float* ctx_wts, int32_t n_ctx,
                               const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out, ctr_callback cb, void* user,
-                              ctr_ticket* ticket) {
+                              ctr_ticket* ticket, bool want_sort = false, int32_t* order_out = nullptr, bool* sorted = nullptr) {
     if (!e || !ticket) return fail(CTR_ERR_INVALID, std::string(who) + ": null argument");
     if (!e->loaded || e->shutting_down) return fail(CTR_ERR_STATE, std::string(who) + ": weights not loaded or engine shutting down");
     if (n_cand < 0 || (n_cand > 0 && (!ids || !wts || !scores_out))) return fail(CTR_ERR_INVALID, std::string(who) + ": null buffer or negative count");
@@ -222,12 +222,15 @@ static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx
         return CTR_OK;
     }
     req->pending = shards;
+    const bool sort_in_stream = want_sort && shards == 1;    // a one-shard request is sorted on its own stream
+    if (sorted) *sorted = sort_in_stream;
     const int Fk = e->m.F - n_ctx;
     for (int i = 0; i < P; ++i) {
         if (en[i] == b[i]) continue;
         Task t;
         t.req = req; t.ids = ids + b[i] * Fk; t.wts = wts + b[i] * Fk; t.n = en[i] - b[i]; t.scores = scores_out + b[i];
         t.ctx_ids = ctx_ids; t.ctx_wts = ctx_wts; t.n_ctx = n_ctx;
+        t.sort = sort_in_stream; t.order_out = order_out;
         DeviceCtx& dc = *e->devs[(first + i) % G];
         {
             std::lock_guard<std::mutex> lk(dc.q_mu);
@@ -282,52 +285,39 @@ int32_t ctr_predict(ctr_engine* e, const int64_t* ids, const float* wts, int64_t
     return ctr_wait(e, t, -1);
 }
 
-// DC:195 on the device.  The merged scores (host) go to device 0 of the engine, are sorted there with
-// their candidate indices, and come back; 8 bytes per candidate each way next to 468 going in.
+// DC:195 on the device: sorted scores and the candidate index of each.
 int32_t ctr_predict_sorted(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* sorted_scores_out,
                            int32_t* order_out) {
     if (!e || (n_cand > 0 && !sorted_scores_out)) return fail(CTR_ERR_INVALID, "ctr_predict_sorted: null argument");
     if (n_cand > INT32_MAX / 2) return fail(CTR_ERR_CAPACITY, "ctr_predict_sorted: too many candidates");
-    int32_t rc = ctr_predict(e, ids, wts, n_cand, sorted_scores_out);          // unsorted, ordered merge (DC:161-164)
-    if (rc != CTR_OK || n_cand == 0) return rc;
+    // One shard (one GPU, or a request below the fan-out threshold): scored and sorted on the same stream,
+    // one round trip.  Several shards: ordered merge on the host first (DC:161-164), then the sort on GPU 0.
+    ctr_ticket tk;
+    bool sorted = false;
+    int32_t rc = submit_request(e, "ctr_predict_sorted", nullptr, nullptr, 0, ids, wts, n_cand, sorted_scores_out, nullptr, nullptr, &tk,
+                                true, order_out, &sorted);
+    if (rc != CTR_OK) return rc;
+    rc = ctr_wait(e, tk, -1);
+    if (rc != CTR_OK || n_cand == 0 || sorted) return rc;
     DeviceCtx& dc = *e->devs[0];
     std::lock_guard<std::mutex> lk(dc.sort_mu);
     CUDA_TRY(cudaSetDevice(dc.model.dev));
     const int n = (int)n_cand;
-    const int n_blocks = (n + kSortTile - 1) / kSortTile;
     if (dc.sort_cap < n_cand) {
-        if (dc.sort_cap) {
-            cudaFree(dc.srt_scores); cudaFree(dc.srt_sorted); cudaFree(dc.srt_counts);
-            for (int i = 0; i < 2; ++i) { cudaFree(dc.srt_keys[i]); cudaFree(dc.srt_idx[i]); }
-            dc.sort_cap = 0;
-        }
         const int64_t cap = std::max<int64_t>(n_cand, e->cfg.max_candidates * (int64_t)e->cfg.n_devices);
+        cudaFree(dc.srt_scores);
+        dc.srt_scores = nullptr;
+        dc.sort_cap = 0;
         CUDA_TRY(cudaMalloc(&dc.srt_scores, cap * sizeof(float)));
-        CUDA_TRY(cudaMalloc(&dc.srt_sorted, cap * sizeof(float)));
-        for (int i = 0; i < 2; ++i) {
-            CUDA_TRY(cudaMalloc(&dc.srt_keys[i], cap * sizeof(uint32_t)));
-            CUDA_TRY(cudaMalloc(&dc.srt_idx[i], cap * sizeof(int32_t)));
-        }
-        CUDA_TRY(cudaMalloc(&dc.srt_counts, (size_t)256 * ((cap + kSortTile - 1) / kSortTile) * sizeof(uint32_t)));
+        if ((rc = alloc_sort_bufs(dc.srt, cap)) != CTR_OK) return rc;
         dc.sort_cap = cap;
     }
     cudaStream_t st = dc.main_stream;
     CUDA_TRY(cudaMemcpyAsync(dc.srt_scores, sorted_scores_out, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, st));
-    const int g1 = std::max(1, std::min((n + 255) / 256, dc.model.num_sms * 8));
-    sort_make_keys_kernel<<<g1, 256, 0, st>>>(dc.srt_scores, n, dc.srt_keys[0], dc.srt_idx[0]);
-    int cur = 0;
-    for (int pass = 0; pass < 4; ++pass) {
-        sort_hist_kernel<<<n_blocks, kSortThreads, 0, st>>>(dc.srt_keys[cur], n, pass * 8, dc.srt_counts);
-        sort_scan_kernel<<<1, 1024, 0, st>>>(dc.srt_counts, 256 * n_blocks);
-        sort_scatter_kernel<<<n_blocks, kSortThreads, 0, st>>>(dc.srt_keys[cur], dc.srt_idx[cur], n, pass * 8, dc.srt_counts,
-                                                              dc.srt_keys[cur ^ 1], dc.srt_idx[cur ^ 1]);
-        cur ^= 1;
-    }
-    sort_gather_scores_kernel<<<g1, 256, 0, st>>>(dc.srt_scores, dc.srt_idx[cur], n, dc.srt_sorted);
-    CUDA_TRY(cudaGetLastError());
-    e->launches.fetch_add(14, std::memory_order_relaxed);
-    CUDA_TRY(cudaMemcpyAsync(sorted_scores_out, dc.srt_sorted, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, st));
-    if (order_out) CUDA_TRY(cudaMemcpyAsync(order_out, dc.srt_idx[cur], (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    const int32_t* d_order = nullptr;
+    if ((rc = launch_sort(e, dc.model, dc.srt, dc.srt_scores, n, st, &d_order)) != CTR_OK) return rc;
+    CUDA_TRY(cudaMemcpyAsync(sorted_scores_out, dc.srt.sorted, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, st));
+    if (order_out) CUDA_TRY(cudaMemcpyAsync(order_out, d_order, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return CTR_OK;
 }

@@ -30,6 +30,15 @@ struct Chain {
     ChainParams params;       // template: M / score pointer are filled per launch
 };
 
+// Device buffers of one sort (csrc/sort.cuh): capacity `cap` candidates.
+struct SortBufs {
+    int64_t cap = 0;
+    float* sorted = nullptr;
+    uint32_t* keys[2] = {nullptr, nullptr};
+    int32_t* idx[2] = {nullptr, nullptr};
+    uint32_t* counts = nullptr;
+};
+
 // One stream with its private activation buffers ("slot"): everything a shard needs on the device.
 struct Slot {
     int dev = -1;
@@ -46,6 +55,8 @@ struct Slot {
     std::vector<Chain> chains;
     // pinned staging for pageable callers
     int64_t* h_ids = nullptr; float* h_wts = nullptr; float* h_scores = nullptr; int32_t* h_err = nullptr;
+    SortBufs srt;              // host-request slots: the sort of a one-shard request runs on this slot's stream
+    int32_t* h_order = nullptr;
     // stage timing: a ring of event sets, one set per timed call (first chunk of the call only)
     static constexpr int kTimeSets = 32, kTimeMarks = 12;
     cudaEvent_t (*tev)[kTimeMarks] = nullptr;      // [kTimeSets][kTimeMarks], created when timing is switched on
@@ -73,6 +84,9 @@ struct Task {
     // shared-context request: the first n_ctx fields of every candidate come from one shared list and
     // ids / wts hold only the remaining F - n_ctx fields per candidate
     const int64_t* ctx_ids = nullptr; const float* ctx_wts = nullptr; int32_t n_ctx = 0;
+    // A6 (DC:195) on the shard's own stream: scores come back sorted, order_out (may be null) gets the
+    // candidate index of each.  Only set on requests that run as ONE shard.
+    bool sort = false; int32_t* order_out = nullptr;
     bool stop = false;
 };
 
@@ -86,8 +100,8 @@ struct DeviceCtx {
     // device sort scratch (ctr_predict_sorted), allocated on first use
     std::mutex sort_mu;
     int64_t sort_cap = 0;
-    float* srt_scores = nullptr; float* srt_sorted = nullptr; uint32_t* srt_keys[2] = {nullptr, nullptr};
-    int32_t* srt_idx[2] = {nullptr, nullptr}; uint32_t* srt_counts = nullptr;
+    float* srt_scores = nullptr;
+    SortBufs srt;
     std::deque<Task> queue;
     std::atomic<int> queued{0};                       // queue.size(), readable without q_mu (workers poll it briefly before sleeping)
     std::mutex q_mu;

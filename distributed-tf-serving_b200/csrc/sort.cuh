@@ -2,7 +2,8 @@
 // the device: ascending in Float.compareTo order (-0.0 < +0.0, every NaN last), and -- what the
 // reference's sort throws away -- the candidate index of every sorted score.
 //
-// LSD radix sort, 4 passes of 8 bits over (key, index) pairs, each pass = histogram per tile,
+// Requests of up to 32 768 candidates: the whole sort in one block and one launch (end of this file).
+// Larger: LSD radix sort, 4 passes of 8 bits over (key, index) pairs, each pass = histogram per tile,
 // one-block exclusive scan, stable scatter.  Integer work: results are bit-exact with the oracle
 // (oracle/dcn_client.py::java_float_sort_key + a stable argsort).  HBM-bound, but tiny next to
 // the scoring (8 bytes per candidate per pass); it exists for completeness of the timed region
@@ -113,6 +114,84 @@ __global__ void __launch_bounds__(kSortThreads) sort_scatter_kernel(const uint32
 
 __global__ void sort_gather_scores_kernel(const float* scores, const int32_t* idx, int n, float* sorted) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) sorted[i] = scores[idx[i]];
+}
+
+// ------------------------------------------------------------------ one request's worth: a single CTA
+// Up to kBlockSortMax candidates (the reference's 1 500, config 2's 10 000) are sorted by ONE block in ONE
+// launch: the same 4 x 8-bit LSD passes, but histogram, scan and stable scatter of every pass run inside
+// the block (14 dependent launches of the multi-block path cost ~110 us of launch latency for 10 000
+// candidates; this is ~20 us).  Stability inside a 1024-element tile: __match_any_sync gives each element
+// its rank among the equal digits of its warp, a [warp][digit] count table gives the warps' offsets.
+// The (key, index) arrays ping-pong through global memory (L2-resident at this size).
+constexpr int kBlockSortMax = 32768;
+constexpr int kBlockSortThreads = 1024;
+
+__global__ void __launch_bounds__(kBlockSortThreads) sort_block_kernel(const float* scores, int n, uint32_t* keys0, int32_t* idx0, uint32_t* keys1,
+                                                                       int32_t* idx1, float* sorted) {
+    __shared__ uint32_t warp_cnt[32][256];      // per tile: count, then exclusive prefix over the warps, per digit
+    __shared__ uint32_t base[256];              // where the next element of each digit goes
+    __shared__ uint32_t part[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < n; i += kBlockSortThreads) { keys0[i] = java_sort_key(scores[i]); idx0[i] = i; }
+    __syncthreads();
+    for (int pass = 0; pass < 4; ++pass) {
+        const uint32_t* ksrc = (pass & 1) ? keys1 : keys0;
+        const int32_t* isrc = (pass & 1) ? idx1 : idx0;
+        uint32_t* kdst = (pass & 1) ? keys0 : keys1;
+        int32_t* idst = (pass & 1) ? idx0 : idx1;
+        const int shift = pass * 8;
+        // histogram of the whole array, then its exclusive scan -> base
+        if (tid < 256) base[tid] = 0;
+        __syncthreads();
+        for (int i = tid; i < n; i += kBlockSortThreads) atomicAdd(&base[(ksrc[i] >> shift) & 255u], 1u);
+        __syncthreads();
+        uint32_t mine = 0, incl = 0;
+        if (tid < 256) {
+            mine = base[tid];
+            incl = mine;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            if (lane == 31) part[warp] = incl;
+        }
+        __syncthreads();
+        if (tid < 256) {
+            uint32_t before = 0;
+            for (int w = 0; w < warp; ++w) before += part[w];
+            base[tid] = before + incl - mine;
+        }
+        __syncthreads();
+        // stable scatter, a tile of 1024 elements at a time, in order
+        for (int t0 = 0; t0 < n; t0 += kBlockSortThreads) {
+            const int i = t0 + tid;
+            const bool valid = i < n;
+            const uint32_t key = valid ? ksrc[i] : 0u;
+            const uint32_t dgt = valid ? (key >> shift) & 255u : 256u;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) (&warp_cnt[0][0])[tid + q * kBlockSortThreads] = 0;
+            __syncthreads();
+            const uint32_t peers = __match_any_sync(0xFFFFFFFFu, dgt);
+            const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+            if (valid && rank == 0) warp_cnt[warp][dgt] = __popc(peers);
+            __syncthreads();
+            uint32_t tile_total = 0;
+            if (tid < 256) {
+                for (int w = 0; w < 32; ++w) { const uint32_t c = warp_cnt[w][tid]; warp_cnt[w][tid] = tile_total; tile_total += c; }
+            }
+            __syncthreads();
+            if (valid) {
+                const uint32_t pos = base[dgt] + warp_cnt[warp][dgt] + rank;
+                kdst[pos] = key;
+                idst[pos] = isrc[i];
+            }
+            __syncthreads();
+            if (tid < 256) base[tid] += tile_total;
+        }
+        __syncthreads();
+    }
+    for (int i = tid; i < n; i += kBlockSortThreads) sorted[i] = scores[idx0[i]];       // 4 passes: the result is back in (keys0, idx0)
 }
 
 }  // namespace ctr

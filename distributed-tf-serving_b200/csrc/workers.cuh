@@ -57,9 +57,19 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
         }
         int32_t rc = score_on_slot(e, dc, s, s.d_ids, s.d_wts, t.n, s.d_scores);
         if (rc != CTR_OK) return rc;
-        CUDA_TRY(cudaMemcpyAsync(dst_scores, s.d_scores, sb, cudaMemcpyDeviceToHost, s.stream));
+        const float* d_result = s.d_scores;
+        if (t.sort) {                                          // DC:195 before the scores leave the device
+            const int32_t* d_order = nullptr;
+            if ((rc = alloc_sort_bufs(s.srt, s.cap)) != CTR_OK) return rc;
+            if (!s.h_order) CUDA_TRY(cudaMallocHost(&s.h_order, (size_t)s.cap * sizeof(int32_t)));
+            if ((rc = launch_sort(e, dc.model, s.srt, s.d_scores, (int)t.n, s.stream, &d_order)) != CTR_OK) return rc;
+            d_result = s.srt.sorted;
+            if (t.order_out) CUDA_TRY(cudaMemcpyAsync(s.h_order, d_order, (size_t)t.n * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+        }
+        CUDA_TRY(cudaMemcpyAsync(dst_scores, d_result, sb, cudaMemcpyDeviceToHost, s.stream));
         CUDA_TRY(cudaMemcpyAsync(s.h_err, s.d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         CUDA_TRY(cudaStreamSynchronize(s.stream));
+        if (t.sort && t.order_out) memcpy(t.order_out, s.h_order, (size_t)t.n * sizeof(int32_t));
         if (*s.h_err) {
             CUDA_TRY(cudaMemsetAsync(s.d_err, 0, sizeof(int32_t), s.stream));
             return fail(CTR_ERR_INVALID, "feature id out of range for a direct-indexed table");
@@ -117,8 +127,8 @@ void free_device_state(ctr_engine* e) {
         dc.dev_slots.clear();
         if (dc.model.dev >= 0) free_model(dc.model);
         if (dc.sort_cap) {
-            cudaFree(dc.srt_scores); cudaFree(dc.srt_sorted); cudaFree(dc.srt_counts);
-            for (int i = 0; i < 2; ++i) { cudaFree(dc.srt_keys[i]); cudaFree(dc.srt_idx[i]); }
+            cudaFree(dc.srt_scores);
+            free_sort_bufs(dc.srt);
             dc.sort_cap = 0;
         }
     }
