@@ -215,6 +215,7 @@ def main():
     ap.add_argument("--requests-per-step", type=int, default=64)
     ap.add_argument("--ref-requests-per-step", type=int, default=2)
     ap.add_argument("--rows-per-field", type=int, default=1 << 22)
+    ap.add_argument("--workers", type=int, default=6, help="host worker threads (one stream each) of the engine: the reference's threadPool")
     ap.add_argument("--model", default="wide_deep", choices=sorted(MODELS), help="wide_deep is the headline (config 2); others are secondary runs")
     ap.add_argument("--table-dtype", default="fp32", choices=["fp32", "f16"])
     ap.add_argument("--hashed", action="store_true", help="row = mix64(id) & (V-1) (config 4)")
@@ -264,7 +265,7 @@ def main():
         args.no_cpu_baseline = True                      # the CPU baseline is for the headline configuration
     C, R = args.candidates, args.requests_per_step
     n = C * R
-    eng = binding.Engine(device_ids=(local_rank,), max_candidates=32768, workers_per_device=4)
+    eng = binding.Engine(device_ids=(local_rank,), max_candidates=32768, workers_per_device=args.workers)
     info = eng.load_weights(wpath)
     d_ids, d_wts = device_inputs(torch, n, args.rows_per_field, 4321 + rank)
     d_out = torch.empty(n, dtype=torch.float32, device="cuda")
@@ -347,7 +348,7 @@ def main():
         t_e2e = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": world * n * args.steps / t_e2e, "unit": "candidates/s", "h2d_bytes_per_step": n * F * 12,
                "d2h_bytes_per_step": n * 4, "ms_per_step": t_e2e / args.steps * 1e3,
-               "how": "R ctr_predict_async + ctr_wait per step from pinned host buffers, 4 worker streams"}
+               "how": "R ctr_predict_async + ctr_wait per step from pinned host buffers, %d worker streams" % args.workers}
         assert np.array_equal(pin_o.array[:C], d_out[:C].cpu().numpy()), "host path and device path disagree"
         # request latency (reference window DC:141 -> DC:198 without the sort): one 10k request at a time
         ts = []
