@@ -111,6 +111,8 @@ struct DeviceCtx {
 
 }  // namespace
 
+constexpr size_t kKeepCalledBack = 4096;
+
 struct ctr_engine {
     ctr_config cfg;
     ModelDesc m;
@@ -120,6 +122,7 @@ struct ctr_engine {
     std::vector<std::unique_ptr<DeviceCtx>> devs;
     std::mutex t_mu;
     std::unordered_map<ctr_ticket, std::shared_ptr<Request>> tickets;
+    std::deque<ctr_ticket> called_back;     // completed requests that had a callback, oldest first (guarded by t_mu)
     std::atomic<int64_t> next_ticket{1};
     std::atomic<int64_t> launches{0};
     std::mutex pin_mu;

@@ -18,7 +18,17 @@ void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t st
             r->done_flag.store(true, std::memory_order_release);
         }
         r->cv.notify_all();
-        if (r->cb) r->cb(r->user, r->ticket, r->status.load());
+        if (r->cb) {
+            r->cb(r->user, r->ticket, r->status.load());
+            // A caller that completes its future in the callback never calls ctr_wait: release such tickets
+            // here, keeping the most recent ones so that a wait after the callback still finds its ticket.
+            std::lock_guard<std::mutex> lk(e->t_mu);
+            e->called_back.push_back(r->ticket);
+            while (e->called_back.size() > kKeepCalledBack) {
+                e->tickets.erase(e->called_back.front());
+                e->called_back.pop_front();
+            }
+        }
     }
 }
 

@@ -101,9 +101,9 @@ typedef struct ctr_model_info {
 int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out);
 
 /* ---- the request: replaces processARequest (DC:137-203) minus the sort ----
- * Splits n_cand candidates over the engine's devices by the reference rule
- * (range = n_cand / n_devices, remainder to the last shard; DC:46-55 applied to
- * candidates), scores every shard on its device (sendRequest, DC:91-115) and writes
+ * Splits n_cand candidates over P of the engine's devices (P from ctr_config.
+ * min_shard_candidates, at most n_devices) by the reference rule (range = n_cand / P,
+ * remainder to the last shard; DC:46-55 applied to candidates), scores every shard on its device (sendRequest, DC:91-115) and writes
  * scores_out[j] for candidate j (ordered merge, DC:161-164).  Does not block on the GPU:
  * returns a ticket at once.  ids / wts / scores_out stay owned by the caller and must
  * stay valid until the ticket completes; ids/wts may be shared read-only between
@@ -125,7 +125,10 @@ int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const fl
                                  ctr_callback cb, void* user, ctr_ticket* ticket);
 
 /* Blocks like CompletableFuture.join (DC:158-159).  timeout_ms < 0 waits for ever.  On
- * CTR_OK or a failure status the ticket is released; on CTR_ERR_TIMEOUT it stays valid. */
+ * CTR_OK or a failure status the ticket is released; on CTR_ERR_TIMEOUT it stays valid.
+ * A request submitted with a callback needs no ctr_wait: the engine releases its ticket by
+ * itself (it keeps the 4096 most recently called-back tickets, so a ctr_wait issued soon
+ * after the callback still succeeds). */
 int32_t ctr_wait(ctr_engine* e, ctr_ticket ticket, int32_t timeout_ms);
 
 /* Synchronous convenience: ctr_predict_async + ctr_wait. */
