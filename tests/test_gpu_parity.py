@@ -356,6 +356,38 @@ def test_callback_and_timeout(binding, om, weight_file):
     e.close()
 
 
+def test_called_back_tickets_are_released(binding, om, weight_file):
+    """A caller that completes its future in the callback never waits (the open-loop driver, the Java
+    shim): the engine releases those tickets itself, keeping the 4096 most recent for a late ctr_wait."""
+    import threading
+    w = make_case(om.LR)
+    e = _engine(binding, weight_file(w), max_candidates=64)
+    ids, wts = om.criteo_inputs(8, rows_per_field=1 << 10)
+    total = 4096 + 300
+    left = threading.Semaphore(0)
+    bad = []
+
+    def cb(ticket, status):
+        if status != 0:
+            bad.append((ticket, status))
+        left.release()
+    outs = [np.empty(8, np.float32) for _ in range(64)]
+    tickets = []
+    for i in range(total):
+        if i >= 64:
+            assert left.acquire(timeout=30)                                 # at most 64 in flight: outs[] slots are reused
+        tickets.append(e.predict_async(ids, wts, out=outs[i % 64], callback=cb)[0])
+    for _ in range(64):
+        assert left.acquire(timeout=30)
+    assert not bad
+    e.wait(tickets[-1])                                                     # a recent one is still there
+    with pytest.raises(binding.CtrError) as ei:                             # the oldest were released by the engine
+        e.wait(tickets[0])
+    assert ei.value.code == -4
+    assert np.array_equal(outs[(total - 1) % 64], e.predict(ids, wts))
+    e.close()
+
+
 # ---------------------------------------------------------------- odd shapes: padding paths
 @pytest.mark.parametrize("kind_name,F,hidden,n_cross", [
     ("wide_deep", 48, (200,), 0),             # widest field count, one hidden layer padded 200 -> 256
