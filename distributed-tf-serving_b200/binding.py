@@ -24,7 +24,8 @@ EXPORTS = ["ctr_engine_create", "ctr_engine_destroy", "ctr_engine_load_weights",
            "ctr_score_device", "ctr_partition_bounds", "ctr_last_error", "ctr_abi_version",
            "ctr_engine_launch_count", "ctr_engine_set_timing", "ctr_engine_stage_ms", "ctr_debug_read_rows",
            "ctr_debug_gemm", "ctr_debug_gather", "ctr_score_device_static", "ctr_predict_sorted", "ctr_predict_wire",
-           "ctr_wire_parse_request", "ctr_wire_build_response", "ctr_predict_shared_async"]
+           "ctr_wire_parse_request", "ctr_wire_build_response", "ctr_predict_shared_async", "ctr_predict_packed_async",
+           "ctr_pack_candidates"]
 
 
 class CtrConfig(C.Structure):
@@ -38,6 +39,10 @@ class CtrModelInfo(C.Structure):
                 ("table_dtype", C.c_int32), ("n_hidden", C.c_int32), ("hidden", C.c_int32 * CTR_MAX_HIDDEN),
                 ("n_cross", C.c_int32), ("d_padded", C.c_int32), ("num_rows", C.c_int64),
                 ("table_bytes_per_device", C.c_int64), ("chunk_rows", C.c_int32), ("reserved", C.c_int32)]
+
+
+class CtrPackedLayout(C.Structure):
+    _fields_ = [("struct_size", C.c_int32), ("n_ctx_fields", C.c_int32), ("weighted_mask", C.c_uint64)]
 
 
 CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int32)
@@ -68,6 +73,8 @@ def load_library() -> C.CDLL:
     lib.ctr_engine_model_info.argtypes = [vp, C.POINTER(CtrModelInfo)]
     lib.ctr_predict_async.argtypes = [vp, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
     lib.ctr_predict_shared_async.argtypes = [vp, vp, vp, i32, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
+    lib.ctr_predict_packed_async.argtypes = [vp, C.POINTER(CtrPackedLayout), vp, vp, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
+    lib.ctr_pack_candidates.argtypes = [vp, C.POINTER(CtrPackedLayout), vp, vp, i64, vp, vp, vp, vp]
     lib.ctr_wait.argtypes = [vp, i64, i32]
     lib.ctr_predict.argtypes = [vp, vp, vp, i64, vp]
     lib.ctr_alloc_pinned.argtypes = [vp, i64, C.POINTER(vp)]
@@ -233,6 +240,52 @@ class Engine:
         _check(self.lib.ctr_predict_shared_async(self.handle, ctx_ids.ctypes.data, ctx_wts.ctypes.data, ctx_ids.size,
                                                  cand_ids.ctypes.data, cand_wts.ctypes.data, n, out.ctypes.data, None, None, C.byref(t)))
         self._keep[t.value] = (ctx_ids, ctx_wts, cand_ids, cand_wts, out)
+        return t.value, out
+
+    @staticmethod
+    def packed_layout(n_ctx_fields: int = 0, weighted_fields=()) -> CtrPackedLayout:
+        """Layout of a packed request: which leading fields are shared context, which fields carry weights."""
+        lay = CtrPackedLayout()
+        lay.struct_size = C.sizeof(CtrPackedLayout)
+        lay.n_ctx_fields = n_ctx_fields
+        lay.weighted_mask = sum(1 << int(f) for f in weighted_fields)
+        return lay
+
+    def pack_candidates(self, layout: CtrPackedLayout, ids, wts, rows_out=None, wts_out=None):
+        """ctr_pack_candidates: reference lists [n, F] -> (ctx_ids, ctx_wts, cand_rows uint32 [n, Fk], cand_wts [n, Wk])."""
+        ids, wts, n = self._check_inputs(ids, wts)
+        nc = layout.n_ctx_fields
+        fk = self.num_fields - nc
+        wk = bin(layout.weighted_mask >> nc & ((1 << fk) - 1)).count("1")
+        rows = rows_out if rows_out is not None else np.empty((n, fk), np.uint32)
+        cw = wts_out if wts_out is not None else np.empty((n, wk), np.float32)
+        ctx_i = np.zeros(max(nc, 1), np.int64)
+        ctx_w = np.zeros(max(nc, 1), np.float32)
+        _check(self.lib.ctr_pack_candidates(self.handle, C.byref(layout), ids.ctypes.data, wts.ctypes.data, n, rows.ctypes.data,
+                                            cw.ctypes.data if wk else None, ctx_i.ctypes.data, ctx_w.ctypes.data))
+        return ctx_i[:nc], ctx_w[:nc], rows, cw
+
+    def predict_packed_async(self, layout: CtrPackedLayout, ctx_ids, ctx_wts, cand_rows, cand_wts, out: Optional[np.ndarray] = None):
+        """Packed request: uint32 table rows, weights only for the layout's weighted fields, optional shared context."""
+        ctx_ids = np.ascontiguousarray(ctx_ids, np.int64)
+        ctx_wts = np.ascontiguousarray(ctx_wts, np.float32)
+        cand_rows = np.asarray(cand_rows)
+        cand_wts = np.asarray(cand_wts)
+        fk = self.num_fields - layout.n_ctx_fields
+        if cand_rows.dtype != np.uint32 or not cand_rows.flags.c_contiguous or cand_rows.size % fk:
+            raise TypeError("cand_rows must be C-contiguous uint32 [n, %d]" % fk)
+        if cand_wts.size and (cand_wts.dtype != np.float32 or not cand_wts.flags.c_contiguous):
+            raise TypeError("cand_wts must be C-contiguous float32")
+        if ctx_ids.size != layout.n_ctx_fields or ctx_wts.size != layout.n_ctx_fields:
+            raise ValueError("context lists need n_ctx_fields entries")
+        n = cand_rows.size // fk
+        if out is None:
+            out = np.empty(n, np.float32)
+        t = C.c_int64()
+        _check(self.lib.ctr_predict_packed_async(self.handle, C.byref(layout), ctx_ids.ctypes.data if ctx_ids.size else None,
+                                                 ctx_wts.ctypes.data if ctx_wts.size else None, cand_rows.ctypes.data,
+                                                 cand_wts.ctypes.data if cand_wts.size else None, n, out.ctypes.data, None, None, C.byref(t)))
+        self._keep[t.value] = (layout, ctx_ids, ctx_wts, cand_rows, cand_wts, out)
         return t.value, out
 
     def wait(self, ticket: int, timeout_ms: int = -1) -> np.ndarray:

@@ -213,6 +213,16 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
                  ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
 }
 
+// Two floats -> packed half2 (lo in the low 16 bits), round to nearest even, SATURATING at +-65504: an
+// activation outside the half range (a raw, un-log-scaled dense feature times its embedding) is clamped
+// instead of becoming +-inf and turning the candidate's score into NaN.  Same cost as the plain pack
+// (SASS F2FP.SATFINITE.F16.F32.PACK_AB).
+__device__ __forceinline__ uint32_t pack_half2_sat(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
 __device__ __forceinline__ float sigmoidf_fast(float z) { return 1.0f / (1.0f + __expf(-z)); }
 
 }  // namespace ctr

@@ -111,7 +111,7 @@ int32_t ctr_debug_gather(ctr_engine* e, int32_t device_index, const int64_t* ids
     CUDA_TRY(cudaMemcpyAsync(s.d_wts, wts, (size_t)n * m.F * sizeof(float), cudaMemcpyHostToDevice, s.stream));
     // run the whole chunk (the gather is its first kernel), then read the gather's outputs back
     s.time_this = false;
-    int32_t rc = score_chunk(e, dc, s, s.d_ids, s.d_wts, (int)n, s.d_scores);
+    int32_t rc = score_chunk(e, dc, s, reference_view(s.d_ids, s.d_wts, m.F), (int)n, s.d_scores);
     if (rc != CTR_OK) return rc;
     CUDA_TRY(cudaStreamSynchronize(s.stream));
     if (x_out && m.kind != CTR_MODEL_LR) {

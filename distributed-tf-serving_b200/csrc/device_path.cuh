@@ -2,29 +2,26 @@
 #pragma once
 namespace {
 // ------------------------------------------------------------------ the device path for one chunk
-template <int TD, bool H, bool E, bool L, bool FM, bool S>
-void launch_gather_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
-    gather_pool_kernel<TD, H, E, L, FM, S><<<grid, kGatherThreads, smem, st>>>(gp);
-}
-
-template <int TD, bool H, bool S>
+template <int TD, int IT, bool C>
 void launch_gather_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
     switch (kind) {
-        case CTR_MODEL_LR: launch_gather_t<TD, H, false, true, false, S>(gp, grid, smem, st); break;
-        case CTR_MODEL_WIDE_DEEP: launch_gather_t<TD, H, true, true, false, S>(gp, grid, smem, st); break;
-        case CTR_MODEL_DEEPFM: launch_gather_t<TD, H, true, true, true, S>(gp, grid, smem, st); break;
-        default: launch_gather_t<TD, H, true, false, false, S>(gp, grid, smem, st); break;
+        case CTR_MODEL_LR: gather_pool_kernel<TD, IT, C, false, true, false><<<grid, kGatherThreads, smem, st>>>(gp); break;
+        case CTR_MODEL_WIDE_DEEP: gather_pool_kernel<TD, IT, C, true, true, false><<<grid, kGatherThreads, smem, st>>>(gp); break;
+        case CTR_MODEL_DEEPFM: gather_pool_kernel<TD, IT, C, true, true, true><<<grid, kGatherThreads, smem, st>>>(gp); break;
+        default: gather_pool_kernel<TD, IT, C, true, false, false><<<grid, kGatherThreads, smem, st>>>(gp); break;
     }
 }
 
-void launch_gather(const ModelDesc& m, bool sharded, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
-    const bool hashed = m.id_mode == CTR_ID_HASHED;
+// Load slots per lane and candidate: fp32 rows take 4 rows per load instruction (F <= 40 -> 10 slots, else 12),
+// f16 rows 8 (F <= 40 -> 5 slots, else 6).
+void launch_gather(const ModelDesc& m, bool compact, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    const bool wide = m.F > 40;
     if (m.table_dtype == CTR_TABLE_FP32) {
-        if (sharded) { if (hashed) launch_gather_kind<0, true, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, false, true>(m.kind, gp, grid, smem, st); }
-        else { if (hashed) launch_gather_kind<0, true, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, false, false>(m.kind, gp, grid, smem, st); }
+        if (compact) { if (wide) launch_gather_kind<0, 12, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 10, true>(m.kind, gp, grid, smem, st); }
+        else { if (wide) launch_gather_kind<0, 12, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 10, false>(m.kind, gp, grid, smem, st); }
     } else {
-        if (sharded) { if (hashed) launch_gather_kind<1, true, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, false, true>(m.kind, gp, grid, smem, st); }
-        else { if (hashed) launch_gather_kind<1, true, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, false, false>(m.kind, gp, grid, smem, st); }
+        if (compact) { if (wide) launch_gather_kind<1, 6, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, 5, true>(m.kind, gp, grid, smem, st); }
+        else { if (wide) launch_gather_kind<1, 6, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, 5, false>(m.kind, gp, grid, smem, st); }
     }
 }
 
@@ -49,33 +46,42 @@ void mark(ctr_engine* e, Slot& s, int stage) {
     if (stage == -2) { s.n_marks = s.cur_mark; s.cur_mark = 0; ++s.sets_recorded; s.time_this = false; }
 }
 
-// Scores rows [0, n) of (d_ids, d_wts) into d_scores on s.stream; n <= s.x_rows for tower models.
-int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int n, float* d_scores) {
+// Scores rows [0, n) of the device-side view `in` into d_scores on s.stream; n <= s.x_rows for tower models.
+int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, int n, float* d_scores) {
     const ModelDesc& m = e->m;
     DeviceModel& dm = dc.model;
     cudaStream_t st = s.stream;
     const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1;
+    const bool compact = !in.reference_layout(m.F);
 
     GatherParams gp;
     memset(&gp, 0, sizeof(gp));
-    gp.ids = d_ids; gp.wts = d_wts; gp.n = n; gp.F = m.F;
-    gp.bulk_ok = ((reinterpret_cast<uintptr_t>(d_ids) | reinterpret_cast<uintptr_t>(d_wts)) & 15) == 0;
+    gp.ids = in.ids; gp.wts = in.wts; gp.n = n; gp.F = m.F;
+    gp.Fk = in.Fk; gp.Wk = in.Wk; gp.id_bytes = in.id_bytes; gp.n_ctx = in.n_ctx; gp.weighted_mask = in.weighted_mask;
+    gp.hashed = m.id_mode == CTR_ID_HASHED && !in.ids_are_rows;
+    for (int f = 0; f < in.n_ctx; ++f) {     // context ids always arrive as ids: bring them to what the per-candidate list holds
+        const bool to_row = in.ids_are_rows && m.id_mode == CTR_ID_HASHED;
+        gp.ctx_ids[f] = to_row ? (int64_t)(mix64((uint64_t)in.ctx_ids[f]) & ((uint64_t)m.V - 1)) : in.ctx_ids[f];
+        gp.ctx_wts[f] = in.ctx_wts[f];
+    }
+    gp.bulk_ok = ((reinterpret_cast<uintptr_t>(in.ids) | reinterpret_cast<uintptr_t>(in.wts)) & 15) == 0;
     gp.table = dm.table; gp.num_rows = (uint64_t)m.V; gp.b0 = dm.b0;
     gp.error_flag = s.d_err;
     gp.n_shards = sharded ? e->cfg.n_devices : 1;
     for (int g = 0; g < CTR_MAX_DEVICES; ++g) gp.shard_base[g] = e->shard_base[g];
     if (m.kind == CTR_MODEL_LR) { gp.scores = d_scores; }
     else { gp.X = s.buf[0]; gp.ldx = s.ld[0]; gp.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide; }
-    const int n_tiles = (n + kGatherTile - 1) / kGatherTile;
-    static const int gather_ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : CTR_GATHER_MIN_CTAS; }();
-    const int ggrid = std::max(1, std::min(n_tiles, dm.num_sms * gather_ctas_per_sm));
-    const size_t gsmem = (size_t)2 * kGatherTile * m.F * 12;
+    const int64_t n_tiles = ((int64_t)n + kWarpTile - 1) / kWarpTile;
+    static const int gather_ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : 4; }();
+    const int ggrid = (int)std::max<int64_t>(1, std::min<int64_t>((n_tiles + kGatherWarps - 1) / kGatherWarps, (int64_t)dm.num_sms * gather_ctas_per_sm));
+    const size_t gsmem = (size_t)kGatherWarps * 2 * (in.ids_bytes(kWarpTile) + in.wts_bytes(kWarpTile));
     mark(e, s, 0);
-    launch_gather(m, sharded, gp, ggrid, gsmem, st);
+    launch_gather(m, compact, gp, ggrid, gsmem, st);
     CUDA_TRY(cudaGetLastError());
     e->launches.fetch_add(1, std::memory_order_relaxed);
     int li = 0;
-    static const bool chain_prof = getenv("CTR_CHAIN_PROF") != nullptr;      // bring-up: in-kernel cycle counters to stderr
+    static const bool chain_prof_env = getenv("CTR_CHAIN_PROF") != nullptr;  // bring-up: in-kernel cycle counters to stderr
+    const bool chain_prof = chain_prof_env && s.owns_buffers;                // it allocates: never on the no-allocation path
     for (const Chain& c : s.chains) {
         mark(e, s, ++li);
         long long* d_prof = nullptr;
@@ -84,7 +90,7 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
             CUDA_TRY(cudaMemsetAsync(d_prof, 0, (size_t)dm.num_sms * 8 * sizeof(long long), st));
         }
         int32_t rc = launch_chain(c, s, n, d_scores, dm.num_sms, st, d_prof);
-        if (rc != CTR_OK) return rc;
+        if (rc != CTR_OK) { if (d_prof) cudaFree(d_prof); return rc; }
         e->launches.fetch_add(1, std::memory_order_relaxed);
         if (chain_prof) {
             std::vector<long long> h((size_t)dm.num_sms * 8);
@@ -108,14 +114,13 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids,
     return CTR_OK;
 }
 
-// Scores n candidates (device pointers) on slot s, chunked so activations stay in their buffers.
-int32_t score_on_slot(ctr_engine* e, DeviceCtx& dc, Slot& s, const int64_t* d_ids, const float* d_wts, int64_t n, float* d_scores) {
-    const int F = e->m.F;
+// Scores n candidates (device-side view) on slot s, chunked so activations stay in their buffers.
+int32_t score_on_slot(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, int64_t n, float* d_scores) {
     const int64_t step = e->m.kind == CTR_MODEL_LR ? (int64_t)1 << 30 : s.x_rows;
     for (int64_t c0 = 0; c0 < n; c0 += step) {
         const int cnt = (int)std::min<int64_t>(step, n - c0);
         s.time_this = false;                   // stage timing is for ctr_score_device calls
-        int32_t rc = score_chunk(e, dc, s, d_ids + c0 * F, d_wts + c0 * F, cnt, d_scores + c0);
+        int32_t rc = score_chunk(e, dc, s, in.at(c0), cnt, d_scores + c0);
         if (rc != CTR_OK) return rc;
     }
     return CTR_OK;

@@ -208,10 +208,69 @@ int32_t alloc_sort_bufs(SortBufs& b, int64_t cap) {
     return CTR_OK;
 }
 
+// Sizes and allocates the device's pair scratch for the loaded model.  Buffer 1 takes the outputs of the even MLP
+// layers, buffer 2 of the odd ones (the last layer has no output: its epilogue is the head), each as wide as the
+// widest layer it holds -- 1024 + 512 columns for 624->1024->512->256, not 2 x 1024; buffers 3-5 are DCN-v2's
+// x_l ping-pong and the tile-major copy of x0.
+int32_t alloc_pair_scratch(ctr_engine* e, DeviceCtx& dc) {
+    const ModelDesc& m = e->m;
+    DeviceModel& dm = dc.model;
+    PairScratch& ps = dc.scratch;
+    if (m.kind == CTR_MODEL_LR) return CTR_OK;
+    CUDA_TRY(cudaSetDevice(dm.dev));
+    ps.n_slices = dm.num_sms / 2;
+    const size_t rows = (size_t)ps.n_slices * 2 * 2 * kBM;            // two 256-row tiles in flight per slice
+    for (int l = 0; l + 1 < (int)dm.mlp.size(); ++l) ps.ld[1 + (l & 1)] = std::max(ps.ld[1 + (l & 1)], dm.mlp[l].Npad);
+    if (m.kind == CTR_MODEL_DCN_V2) {
+        const int xl_ld = dm.cross.empty() ? m.d_pad() : dm.cross.back().Npad;      // cross outputs may be padded past d_pad
+        ps.ld[3] = ps.ld[4] = ps.ld[5] = xl_ld;
+    }
+    size_t off[6] = {0, 0, 0, 0, 0, 0}, total = 256;
+    for (int i = 1; i < 6; ++i) { off[i] = total; total += rows * ps.ld[i] * sizeof(__half); }
+    CUDA_TRY(cudaMalloc(&ps.base, total));
+    CUDA_TRY(cudaMemset(ps.base, 0, total));                          // bitmap clear, pad columns zero
+    ps.bytes = total;
+    ps.bitmap = reinterpret_cast<unsigned long long*>(ps.base);
+    for (int i = 1; i < 6; ++i) ps.buf[i] = ps.ld[i] ? reinterpret_cast<__half*>(ps.base + off[i]) : nullptr;
+    // Keep the scratch in L2: it is written and re-read within microseconds by the same SM pair, but anything
+    // streaming through (X, table rows) would push its dirty lines out to HBM and back.  The device sets aside
+    // what it can for persisting lines; each stream's access window (set in init_slot_common) covers the scratch.
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, dm.dev));
+    static const bool no_persist = getenv("CTR_NO_L2_PERSIST") != nullptr;
+    if (!no_persist && prop.persistingL2CacheMaxSize > 0) {
+        const size_t want = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, total);
+        if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) != cudaSuccess) (void)cudaGetLastError();
+        else dc.l2_persist_bytes = want;
+        dc.l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
+    }
+    return CTR_OK;
+}
+
+void free_pair_scratch(DeviceCtx& dc) {
+    if (dc.scratch.base) cudaFree(dc.scratch.base);
+    dc.scratch = PairScratch();
+}
+
+// Points a stream's L2 access-policy window at the device's pair scratch (persisting hits; misses stream).
+void set_scratch_window(DeviceCtx& dc, cudaStream_t st) {
+    const PairScratch& ps = dc.scratch;
+    if (!ps.base || !dc.l2_persist_bytes || !dc.l2_window_max) return;
+    cudaStreamAttrValue v;
+    memset(&v, 0, sizeof(v));
+    v.accessPolicyWindow.base_ptr = ps.base;
+    v.accessPolicyWindow.num_bytes = std::min(ps.bytes, dc.l2_window_max);
+    v.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)dc.l2_persist_bytes / (double)v.accessPolicyWindow.num_bytes);
+    v.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    v.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &v) != cudaSuccess) (void)cudaGetLastError();
+}
+
 void free_slot(Slot& s) {
     cudaSetDevice(s.dev);
-    cudaFree(s.d_ids); cudaFree(s.d_wts); cudaFree(s.d_scores); cudaFree(s.d_cids); cudaFree(s.d_cwts); cudaFree(s.d_wide); cudaFree(s.d_extra); cudaFree(s.d_err);
-    for (auto*& b : s.buf) { cudaFree(b); b = nullptr; }
+    cudaFree(s.d_ids); cudaFree(s.d_wts); cudaFree(s.d_scores); cudaFree(s.d_wide); cudaFree(s.d_extra); cudaFree(s.d_err);
+    cudaFree(s.buf[0]);                        // X; buffers 1-5 are slices of the device's pair scratch
+    for (auto*& b : s.buf) b = nullptr;
     cudaFreeHost(s.h_ids); cudaFreeHost(s.h_wts); cudaFreeHost(s.h_scores); cudaFreeHost(s.h_err); cudaFreeHost(s.h_order);
     free_sort_bufs(s.srt);
     if (s.tev) {
@@ -266,6 +325,7 @@ int32_t build_chains(ctr_engine* e, DeviceModel& dm, Slot& s) {
         c.params.x0 = s.buf[0]; c.params.ldx0 = s.ld[0];
         if (is_cross && c.n_layers > 1) { c.params.x0e = s.buf[5]; c.params.ldx0e = s.ld[5]; }
         c.params.b_out = dm.b_out;
+        c.params.slice_bitmap = s.slice_bitmap; c.params.n_slices = s.n_slices;
         if (is_cross) {
             c.params.extra_out = s.d_extra;                   // w_x . x_L, consumed by the MLP chain's head
         } else {
@@ -286,12 +346,11 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     CUDA_TRY(cudaSetDevice(dm.dev));
     s.cap = e->cfg.max_candidates;
     const int pairs = dm.num_sms / 2;
-    // rows per launch: host-request slots hold one request; device-resident slots default to 16 tiles per
-    // CTA pair (16 x 74 x 256 = 303 104 candidates, X = 388 MB; measured 239 / 264 / 278 / 284 / 293 M cand/s
-    // at 1 / 2 / 4 / 8 / 16 tiles per pair), CTR_CHUNK_ROWS overrides
-    const int want = host_staging ? (int)s.cap : (e->chunk_rows > 0 ? e->chunk_rows : 16 * pairs * 2 * kBM);
+    // rows per launch: host-request slots hold one request; device-resident slots default to 8 tiles per CTA pair
+    // (8 x 74 x 256 = 151 552 candidates, X = 194 MB per slot): small enough that the first chunk's gather, the
+    // only one that runs with nothing to hide under, is a small part of a call; CTR_CHUNK_ROWS overrides
+    const int want = host_staging ? (int)s.cap : (e->chunk_rows > 0 ? e->chunk_rows : 8 * pairs * 2 * kBM);
     s.x_rows = round_up(std::max(want, 1), 2 * kBM);
-    s.scratch_rows = std::min(pairs, s.x_rows / (2 * kBM)) * 2 * kBM;
     CUDA_TRY(cudaMalloc(&s.d_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
     CUDA_TRY(cudaMalloc(&s.d_wts, (size_t)s.cap * m.F * sizeof(float)));
     CUDA_TRY(cudaMalloc(&s.d_scores, (size_t)s.cap * sizeof(float)));
@@ -300,8 +359,6 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     CUDA_TRY(cudaMalloc(&s.d_err, sizeof(int32_t)));
     CUDA_TRY(cudaMemset(s.d_err, 0, sizeof(int32_t)));
     if (host_staging) {
-        CUDA_TRY(cudaMalloc(&s.d_cids, ((size_t)s.cap * m.F + CTR_MAX_FIELDS) * sizeof(int64_t)));
-        CUDA_TRY(cudaMalloc(&s.d_cwts, ((size_t)s.cap * m.F + CTR_MAX_FIELDS) * sizeof(float)));
         CUDA_TRY(cudaMallocHost(&s.h_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
         CUDA_TRY(cudaMallocHost(&s.h_wts, (size_t)s.cap * m.F * sizeof(float)));
         CUDA_TRY(cudaMallocHost(&s.h_scores, (size_t)s.cap * sizeof(float)));
@@ -312,25 +369,15 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     }
     if (m.kind == CTR_MODEL_LR) return CTR_OK;
 
-    const int dpad = m.d_pad();
-    int maxn = 0;
-    for (auto& L : dm.mlp) maxn = std::max(maxn, L.Npad);
-    auto alloc_buf = [&](int id, int rows, int ldv) -> int32_t {
-        s.ld[id] = ldv;
-        CUDA_TRY(cudaMalloc(&s.buf[id], (size_t)rows * ldv * sizeof(__half)));
-        CUDA_TRY(cudaMemset(s.buf[id], 0, (size_t)rows * ldv * sizeof(__half)));   // pad columns stay zero
-        return CTR_OK;
-    };
-    int32_t rc;
-    if ((rc = alloc_buf(0, s.x_rows, dpad)) != CTR_OK) return rc;
-    if ((rc = alloc_buf(1, 2 * s.scratch_rows, maxn)) != CTR_OK) return rc;        // 2 tiles in flight per CTA pair
-    if ((rc = alloc_buf(2, 2 * s.scratch_rows, maxn)) != CTR_OK) return rc;
-    if (m.kind == CTR_MODEL_DCN_V2) {
-        const int xl_ld = dm.cross.empty() ? dpad : dm.cross.back().Npad;      // cross outputs may be padded past d_pad
-        if ((rc = alloc_buf(3, 2 * s.scratch_rows, xl_ld)) != CTR_OK) return rc;
-        if ((rc = alloc_buf(4, 2 * s.scratch_rows, xl_ld)) != CTR_OK) return rc;
-        if ((rc = alloc_buf(5, 2 * s.scratch_rows, xl_ld)) != CTR_OK) return rc;
-    }
+    // X is the slot's own; the layer activations live in the device's pair scratch
+    s.ld[0] = m.d_pad();
+    CUDA_TRY(cudaMalloc(&s.buf[0], (size_t)s.x_rows * s.ld[0] * sizeof(__half)));
+    CUDA_TRY(cudaMemset(s.buf[0], 0, (size_t)s.x_rows * s.ld[0] * sizeof(__half)));   // pad columns stay zero
+    const PairScratch& ps = dc.scratch;
+    for (int i = 1; i < 6; ++i) { s.buf[i] = ps.buf[i]; s.ld[i] = ps.ld[i]; }
+    s.slice_bitmap = ps.bitmap; s.n_slices = ps.n_slices;
+    s.scratch_rows = ps.n_slices * 2 * kBM;
+    set_scratch_window(dc, s.stream);
     return build_chains(e, dm, s);
 }
 

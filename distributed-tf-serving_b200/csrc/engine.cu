@@ -128,7 +128,12 @@ int32_t ctr_engine_destroy(ctr_engine* e) {
 int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
     if (!e || !path) return fail(CTR_ERR_INVALID, "ctr_engine_load_weights: null argument");
     HostWeights hw;
-    int32_t rc = read_weight_file(path, &hw);
+    int32_t rc;
+    try {                                   // nothing may unwind through the C boundary
+        rc = read_weight_file(path, &hw);
+    } catch (const std::exception& ex) {
+        return fail(CTR_ERR_IO, std::string("weight file: ") + ex.what());
+    }
     if (rc != CTR_OK) return rc;
     stop_workers(e);
     free_device_state(e);
@@ -137,6 +142,7 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
     for (int i = 0; i < e->cfg.n_devices; ++i) {
         if ((rc = load_model_on_device(e, i, hw)) != CTR_OK) return rc;
         e->shard_base[i] = e->devs[i]->model.table;
+        if ((rc = alloc_pair_scratch(e, *e->devs[i])) != CTR_OK) return rc;
     }
     for (int i = 0; i < e->cfg.n_devices; ++i) {
         DeviceCtx& dc = *e->devs[i];
@@ -148,9 +154,9 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
             if ((rc = build_slot_plan(e, dc, *s, true)) != CTR_OK) return rc;
             dc.worker_slots.push_back(std::move(s));
         }
-        // one stream by default: gather and tower both fill the machine, and a second stream only
-        // interleaves them (+4% throughput, measured) at the price of blurred per-kernel timing
-        int n_dev_slots = 1;
+        // Two streams, chunks alternating between them: chunk k+1's gather (HBM-bound, one 256-thread CTA per SM fits
+        // beside the resident tower CTA) runs UNDER chunk k's tower (tensor-bound) instead of in front of it.
+        int n_dev_slots = 2;
         if (const char* c = getenv("CTR_DEVICE_STREAMS")) { int v = atoi(c); if (v >= 1 && v <= 8) n_dev_slots = v; }
         for (int w = 0; w < n_dev_slots; ++w) {
             std::unique_ptr<Slot> s(new Slot());
@@ -181,14 +187,31 @@ int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out) {
     return CTR_OK;
 }
 
-static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx_ids, const float* ctx_wts, int32_t n_ctx,
-                              const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out, ctr_callback cb, void* user,
-                              ctr_ticket* ticket, bool want_sort = false, int32_t* order_out = nullptr, bool* sorted = nullptr) {
+// Checks a compact layout against the loaded model and fills the view's derived fields.
+static int32_t make_compact_view(ctr_engine* e, const char* who, int32_t n_ctx, uint64_t weighted_mask, bool narrow_rows, InputView* v) {
+    if (!e) return fail(CTR_ERR_INVALID, std::string(who) + ": null engine");
+    if (!e->loaded) return fail(CTR_ERR_STATE, std::string(who) + ": weights not loaded");
+    const int F = e->m.F;
+    if (n_ctx < 0 || n_ctx >= F) return fail(CTR_ERR_INVALID, std::string(who) + ": the shared context must cover 0 .. F-1 leading fields");
+    const uint64_t field_bits = F >= 64 ? ~0ull : ((1ull << F) - 1ull);
+    const uint64_t cand_bits = field_bits & ~((1ull << n_ctx) - 1ull);
+    v->n_ctx = n_ctx;
+    v->Fk = F - n_ctx;
+    v->weighted_mask = weighted_mask & field_bits;
+    v->Wk = __builtin_popcountll(weighted_mask & cand_bits);
+    v->id_bytes = narrow_rows ? 4 : 8;
+    v->ids_are_rows = narrow_rows;
+    return CTR_OK;
+}
+
+// The request itself (processARequest, DC:137-203): cut the candidates of the host-side view `in` over the
+// devices, queue one shard task per device, hand back a ticket.
+static int32_t submit_request(ctr_engine* e, const char* who, const InputView& in, int64_t n_cand, float* scores_out, ctr_callback cb,
+                              void* user, ctr_ticket* ticket, bool want_sort = false, int32_t* order_out = nullptr, bool* sorted = nullptr) {
     if (!e || !ticket) return fail(CTR_ERR_INVALID, std::string(who) + ": null argument");
     if (!e->loaded || e->shutting_down) return fail(CTR_ERR_STATE, std::string(who) + ": weights not loaded or engine shutting down");
-    if (n_cand < 0 || (n_cand > 0 && (!ids || !wts || !scores_out))) return fail(CTR_ERR_INVALID, std::string(who) + ": null buffer or negative count");
-    if (n_ctx < 0 || n_ctx >= e->m.F || (n_ctx > 0 && (!ctx_ids || !ctx_wts)))
-        return fail(CTR_ERR_INVALID, std::string(who) + ": the shared context must cover 0 .. F-1 leading fields");
+    if (n_cand < 0 || (n_cand > 0 && (!in.ids || (in.Wk > 0 && !in.wts) || !scores_out))) return fail(CTR_ERR_INVALID, std::string(who) + ": null buffer or negative count");
+    if (in.n_ctx > 0 && (!in.ctx_ids || !in.ctx_wts)) return fail(CTR_ERR_INVALID, std::string(who) + ": null context list");
     // How many GPUs this request is cut over.  The reference always cuts hostsList.size() ways (DC:38,
     // DC:148); scores do not depend on the cut, and for a small request the fan-out only costs host
     // work and tail latency (8 GPUs, 64-4096 candidates: p99 0.42-0.5 ms against 0.16 on one GPU), so a
@@ -205,7 +228,7 @@ static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx
     split_bounds(n_cand, P, b, en);
     for (int i = 0; i < P; ++i)
         if (en[i] - b[i] > e->cfg.max_candidates)
-            return fail(CTR_ERR_CAPACITY, std::string(who) + ": a shard exceeds max_candidates of this engine");
+            return fail(CTR_ERR_CAPACITY, std::string(who) + ": the last shard (it takes the remainder, DC:46-55) exceeds max_candidates of this engine");
     auto req = std::make_shared<Request>();
     req->cb = cb; req->user = user;
     req->ticket = e->next_ticket.fetch_add(1);
@@ -224,12 +247,10 @@ static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx
     req->pending = shards;
     const bool sort_in_stream = want_sort && shards == 1;    // a one-shard request is sorted on its own stream
     if (sorted) *sorted = sort_in_stream;
-    const int Fk = e->m.F - n_ctx;
     for (int i = 0; i < P; ++i) {
         if (en[i] == b[i]) continue;
         Task t;
-        t.req = req; t.ids = ids + b[i] * Fk; t.wts = wts + b[i] * Fk; t.n = en[i] - b[i]; t.scores = scores_out + b[i];
-        t.ctx_ids = ctx_ids; t.ctx_wts = ctx_wts; t.n_ctx = n_ctx;
+        t.req = req; t.in = in.at(b[i]); t.n = en[i] - b[i]; t.scores = scores_out + b[i];
         t.sort = sort_in_stream; t.order_out = order_out;
         DeviceCtx& dc = *e->devs[(first + i) % G];
         {
@@ -244,13 +265,70 @@ static int32_t submit_request(ctr_engine* e, const char* who, const int64_t* ctx
 
 int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, int64_t n_cand, float* scores_out,
                           ctr_callback cb, void* user, ctr_ticket* ticket) {
-    return submit_request(e, "ctr_predict_async", nullptr, nullptr, 0, ids, wts, n_cand, scores_out, cb, user, ticket);
+    if (!e) return fail(CTR_ERR_INVALID, "ctr_predict_async: null engine");
+    return submit_request(e, "ctr_predict_async", reference_view(ids, wts, e->m.F), n_cand, scores_out, cb, user, ticket);
 }
 
 int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const float* ctx_wts, int32_t n_ctx_fields,
                                  const int64_t* cand_ids, const float* cand_wts, int64_t n_cand, float* scores_out,
                                  ctr_callback cb, void* user, ctr_ticket* ticket) {
-    return submit_request(e, "ctr_predict_shared_async", ctx_ids, ctx_wts, n_ctx_fields, cand_ids, cand_wts, n_cand, scores_out, cb, user, ticket);
+    InputView v;
+    int32_t rc = make_compact_view(e, "ctr_predict_shared_async", n_ctx_fields, ~0ull, false, &v);
+    if (rc != CTR_OK) return rc;
+    v.ids = cand_ids; v.wts = cand_wts; v.ctx_ids = ctx_ids; v.ctx_wts = ctx_wts;
+    return submit_request(e, "ctr_predict_shared_async", v, n_cand, scores_out, cb, user, ticket);
+}
+
+int32_t ctr_predict_packed_async(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ctx_ids, const float* ctx_wts,
+                                 const uint32_t* cand_rows, const float* cand_wts, int64_t n_cand, float* scores_out,
+                                 ctr_callback cb, void* user, ctr_ticket* ticket) {
+    if (!layout || layout->struct_size != (int32_t)sizeof(ctr_packed_layout)) return fail(CTR_ERR_INVALID, "ctr_predict_packed_async: ctr_packed_layout missing or of the wrong size (ABI)");
+    InputView v;
+    int32_t rc = make_compact_view(e, "ctr_predict_packed_async", layout->n_ctx_fields, layout->weighted_mask, true, &v);
+    if (rc != CTR_OK) return rc;
+    if ((uint64_t)e->m.V > 0xFFFFFFFFull) return fail(CTR_ERR_CAPACITY, "ctr_predict_packed_async: the table has more than 2^32 - 1 rows, 32-bit row indices cannot address it");
+    v.ids = cand_rows; v.wts = cand_wts; v.ctx_ids = ctx_ids; v.ctx_wts = ctx_wts;
+    return submit_request(e, "ctr_predict_packed_async", v, n_cand, scores_out, cb, user, ticket);
+}
+
+// The marshaller for the packed layout (what replaces the addAllInt64Val / addAllFloatVal loops of DC:97-108 for a
+// caller that keeps the reference's lists): pure host code.
+int32_t ctr_pack_candidates(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ids, const float* wts, int64_t n_cand,
+                            uint32_t* cand_rows_out, float* cand_wts_out, int64_t* ctx_ids_out, float* ctx_wts_out) {
+    if (!layout || layout->struct_size != (int32_t)sizeof(ctr_packed_layout)) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: ctr_packed_layout missing or of the wrong size (ABI)");
+    InputView v;
+    int32_t rc = make_compact_view(e, "ctr_pack_candidates", layout->n_ctx_fields, layout->weighted_mask, true, &v);
+    if (rc != CTR_OK) return rc;
+    if (n_cand < 0 || (n_cand > 0 && (!ids || !wts || !cand_rows_out || (v.Wk > 0 && !cand_wts_out)))) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: null buffer or negative count");
+    if (v.n_ctx > 0 && n_cand > 0 && (!ctx_ids_out || !ctx_wts_out)) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: null context output");
+    const ModelDesc& m = e->m;
+    if ((uint64_t)m.V > 0xFFFFFFFFull) return fail(CTR_ERR_CAPACITY, "ctr_pack_candidates: the table has more than 2^32 - 1 rows");
+    const int F = m.F, nc = v.n_ctx, Fk = v.Fk, Wk = v.Wk;
+    const bool hashed = m.id_mode == CTR_ID_HASHED;
+    const uint64_t row_mask = (uint64_t)m.V - 1;
+    int wcol[CTR_MAX_FIELDS];                 // per-candidate field (0-based after the context) of every weight column
+    int nw = 0;
+    for (int j = 0; j < Fk; ++j) if ((v.weighted_mask >> (nc + j)) & 1ull) wcol[nw++] = j;
+    for (int f = 0; f < nc && n_cand > 0; ++f) { ctx_ids_out[f] = ids[f]; ctx_wts_out[f] = wts[f]; }
+    for (int64_t b = 0; b < n_cand; ++b) {
+        const int64_t* idr = ids + b * F;
+        const float* wtr = wts + b * F;
+        for (int f = 0; f < nc; ++f)
+            if (idr[f] != ids[f] || memcmp(&wtr[f], &wts[f], sizeof(float)) != 0)
+                return fail(CTR_ERR_INVALID, "ctr_pack_candidates: context field " + std::to_string(f) + " of candidate " + std::to_string(b) + " differs from candidate 0");
+        uint32_t* ro = cand_rows_out + b * Fk;
+        for (int j = 0; j < Fk; ++j) {
+            const uint64_t id = (uint64_t)idr[nc + j];
+            // a direct id the table cannot hold becomes row 0xFFFFFFFF: the kernel reports it exactly like the reference layout
+            ro[j] = hashed ? (uint32_t)(mix64(id) & row_mask) : (id > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)id);
+            if (!((v.weighted_mask >> (nc + j)) & 1ull) && wtr[nc + j] != 1.0f)
+                return fail(CTR_ERR_INVALID, "ctr_pack_candidates: field " + std::to_string(nc + j) + " of candidate " + std::to_string(b) + " has weight " +
+                                                 std::to_string(wtr[nc + j]) + " but the layout declares it unweighted (1.0)");
+        }
+        float* wo = cand_wts_out + b * Wk;
+        for (int k = 0; k < Wk; ++k) wo[k] = wtr[nc + wcol[k]];
+    }
+    return CTR_OK;
 }
 
 int32_t ctr_wait(ctr_engine* e, ctr_ticket ticket, int32_t timeout_ms) {
@@ -294,7 +372,7 @@ int32_t ctr_predict_sorted(ctr_engine* e, const int64_t* ids, const float* wts, 
     // one round trip.  Several shards: ordered merge on the host first (DC:161-164), then the sort on GPU 0.
     ctr_ticket tk;
     bool sorted = false;
-    int32_t rc = submit_request(e, "ctr_predict_sorted", nullptr, nullptr, 0, ids, wts, n_cand, sorted_scores_out, nullptr, nullptr, &tk,
+    int32_t rc = submit_request(e, "ctr_predict_sorted", reference_view(ids, wts, e->m.F), n_cand, sorted_scores_out, nullptr, nullptr, &tk,
                                 true, order_out, &sorted);
     if (rc != CTR_OK) return rc;
     rc = ctr_wait(e, tk, -1);
@@ -415,13 +493,18 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
     const int used = (int)std::min<int64_t>(n_slots, n_chunks);
     // fork: the engine's streams start after whatever the caller queued on `origin`
     CUDA_TRY(cudaEventRecord(dc.fork_ev, origin));
-    for (int w = 0; w < used; ++w) CUDA_TRY(cudaStreamWaitEvent(dc.dev_slots[w]->stream, dc.fork_ev, 0));
+    for (int w = 0; w < used; ++w) {
+        CUDA_TRY(cudaStreamWaitEvent(dc.dev_slots[w]->stream, dc.fork_ev, 0));
+        // a call on a caller's stream never reads the flag: clear it here so that a bad id of that call cannot
+        // fail a later, clean call on the engine's stream
+        CUDA_TRY(cudaMemsetAsync(dc.dev_slots[w]->d_err, 0, sizeof(int32_t), dc.dev_slots[w]->stream));
+    }
     for (int64_t c = 0; c < n_chunks; ++c) {
         Slot& s = *dc.dev_slots[c % used];
         const int64_t c0 = c * step;
         const int cnt = (int)std::min<int64_t>(step, n_cand - c0);
         if (c == 0) { s.time_this = true; s.cur_mark = 0; }  // stage timing: first chunk (slot 0) only
-        int32_t rc = score_chunk(e, dc, s, ids + c0 * F, wts + c0 * F, cnt, scores + c0);
+        int32_t rc = score_chunk(e, dc, s, reference_view(ids + c0 * F, wts + c0 * F, F), cnt, scores + c0);
         if (rc != CTR_OK) return rc;
     }
     // join: `origin` continues after every engine stream has finished
@@ -435,7 +518,7 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
         for (int w = 0; w < used; ++w) {
             int32_t v = 0;
             CUDA_TRY(cudaMemcpy(&v, dc.dev_slots[w]->d_err, sizeof(v), cudaMemcpyDeviceToHost));
-            if (v) { err = 1; CUDA_TRY(cudaMemset(dc.dev_slots[w]->d_err, 0, sizeof(v))); }
+            if (v) err = 1;
         }
         if (err) return fail(CTR_ERR_INVALID, "feature id out of range for a direct-indexed table");
     }

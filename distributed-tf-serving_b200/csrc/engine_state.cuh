@@ -22,6 +22,35 @@ struct DeviceModel {
     bool loaded = false;
 };
 
+// How the features of a request lie in memory (the same description serves the host side of a shard and the
+// device side of a chunk).  Reference layout (DC:97-108): ids int64 [n, F], wts float [n, F].  Compact layouts
+// (ctr_predict_shared_async / ctr_predict_packed_async): the first n_ctx fields once per request (host lists),
+// per candidate the remaining Fk ids as int64 or uint32 and Wk weights (only the fields in weighted_mask).
+struct InputView {
+    const void* ids = nullptr;
+    const float* wts = nullptr;
+    int Fk = 0, Wk = 0, id_bytes = 8, n_ctx = 0;
+    bool ids_are_rows = false;               // values index the table directly (hashed by the host packer already)
+    uint64_t weighted_mask = ~0ull;
+    const int64_t* ctx_ids = nullptr;        // host memory, n_ctx entries
+    const float* ctx_wts = nullptr;
+    bool reference_layout(int F) const { return n_ctx == 0 && id_bytes == 8 && Fk == F && Wk == F && !ids_are_rows; }
+    InputView at(int64_t c0) const {         // the same view, starting at candidate c0
+        InputView v = *this;
+        v.ids = static_cast<const uint8_t*>(ids) + (size_t)c0 * Fk * id_bytes;
+        v.wts = wts ? wts + (size_t)c0 * Wk : nullptr;
+        return v;
+    }
+    size_t ids_bytes(int64_t n) const { return (size_t)n * Fk * id_bytes; }
+    size_t wts_bytes(int64_t n) const { return (size_t)n * Wk * sizeof(float); }
+};
+
+InputView reference_view(const void* ids, const float* wts, int F) {
+    InputView v;
+    v.ids = ids; v.wts = wts; v.Fk = F; v.Wk = F;
+    return v;
+}
+
 // One launch of tower_chain_kernel: a sequence of layers, each feeding the next.
 struct Chain {
     int BN = 256;
@@ -44,15 +73,17 @@ struct Slot {
     int dev = -1;
     cudaStream_t stream = nullptr;
     bool owns_stream = true;
+    bool owns_buffers = true;  // false: the buffers are slices of the fixed scratch of ctr_score_device_static
     int64_t cap = 0;           // candidate capacity of the id/weight/score buffers
     int x_rows = 0;            // candidates per launch: rows of X / wide / extra (multiple of 256)
     int scratch_rows = 0;      // rows of the per-pair scratch (resident CTA pairs x 256)
-    int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;
-    int64_t* d_cids = nullptr; float* d_cwts = nullptr;     // compact lists of a shared-context request (host slots)
+    int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;   // d_ids / d_wts also take the compact layouts
     float* d_wide = nullptr; float* d_extra = nullptr; int32_t* d_err = nullptr;
     __half* buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     int ld[6] = {0, 0, 0, 0, 0, 0};
     std::vector<Chain> chains;
+    unsigned long long* slice_bitmap = nullptr;    // the device's PairScratch bitmap (nullptr: slices by pair index)
+    int n_slices = 0;
     // pinned staging for pageable callers
     int64_t* h_ids = nullptr; float* h_wts = nullptr; float* h_scores = nullptr; int32_t* h_err = nullptr;
     SortBufs srt;              // host-request slots: the sort of a one-shard request runs on this slot's stream
@@ -80,18 +111,30 @@ struct Request {
 
 struct Task {
     std::shared_ptr<Request> req;
-    const int64_t* ids; const float* wts; int64_t n; float* scores;
-    // shared-context request: the first n_ctx fields of every candidate come from one shared list and
-    // ids / wts hold only the remaining F - n_ctx fields per candidate
-    const int64_t* ctx_ids = nullptr; const float* ctx_wts = nullptr; int32_t n_ctx = 0;
+    InputView in;                 // this shard's features in the caller's (host) memory
+    int64_t n = 0; float* scores = nullptr;
     // A6 (DC:195) on the shard's own stream: scores come back sorted, order_out (may be null) gets the
     // candidate index of each.  Only set on requests that run as ONE shard.
     bool sort = false; int32_t* order_out = nullptr;
     bool stop = false;
 };
 
+// The activation scratch of the tower (tower.cuh): ONE allocation per device, cut into num_sms / 2 slices of
+// 2 x 256 rows.  Every slot (stream) of the device works out of it; the tower's CTA pairs take and return slices
+// themselves, so the footprint that cycles through L2 does not grow with the number of streams.
+struct PairScratch {
+    uint8_t* base = nullptr;           // one cudaMalloc: [bitmap 256 B | buf 1 | buf 2 | buf 3 | buf 4 | buf 5]
+    size_t bytes = 0;
+    unsigned long long* bitmap = nullptr;
+    int n_slices = 0;
+    __half* buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    int ld[6] = {0, 0, 0, 0, 0, 0};
+};
+
 struct DeviceCtx {
     DeviceModel model;
+    PairScratch scratch;
+    size_t l2_persist_bytes = 0, l2_window_max = 0;    // persisting-L2 set-aside of the device / largest access window
     std::vector<std::unique_ptr<Slot>> worker_slots;
     std::vector<std::unique_ptr<Slot>> dev_slots;     // for ctr_score_device
     std::mutex dev_mu;                                // serialises ctr_score_device enqueues per device

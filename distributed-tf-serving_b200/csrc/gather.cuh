@@ -7,19 +7,31 @@
 //     lin[b]   = b0 + sum_f W1[row]*wt           (+ 0.5*sum_k[(sum_f x)^2 - sum_f x^2] for DeepFM)
 //
 // Data layout in HBM ("packed rows"): one table row holds the 16 embedding values AND the
-// first-order weight, so a lookup touches one 128-byte line (fp32: 64 B + 4 B, 3 sectors)
-// or one 64-byte half line (f16: 32 B + 4 B, 2 sectors) instead of two unrelated places.
+// first-order weight, so a lookup is ONE place in DRAM and ONE load instruction:
 //     fp32 row (128 B): [e0..e15 fp32 | w1 fp32 | pad]      f16 row (64 B): [e0..e15 half | w1 fp32 | pad]
+// B200's DRAM moves 64-byte granules: an fp32 row (68 useful bytes) costs two of them, an f16 row one.
 //
-// Mapping: one warp per candidate; lane = g*4 + q.  In round r the 8 lane groups g take
-// fields r*8+g, and the 4 lanes q of a group each load one 128-bit quarter of the 64-byte
-// embedding (fp32) -- coalesced, vectorised, every sector fully used.  All rounds' loads
-// are issued before any is consumed (5-6 independent 128-bit loads in flight per lane).
-// The id / weight lists of a 32-candidate tile are staged into shared memory with one
-// bulk async copy each (cp.async.bulk, SASS UBLKCP) on an mbarrier, double buffered, so
-// the next tile's lists land while this tile's rows are being gathered.  Pooling
-// (first-order sum, FM sums) is a fixed warp-shuffle tree: deterministic, so the same
-// candidate gets bit-identical results on any GPU or shard.
+// Mapping (round 2).  A warp owns "warp tiles" of 4 consecutive candidates and never synchronises
+// with the other warps of its CTA.  A row is fetched by ONE 128-bit load instruction spread over the
+// lanes of a lane group (8 lanes per fp32 row: 4 embedding quarters + the lane that takes w1; 4 lanes
+// per f16 row), so a load instruction touches one 128-byte line per row -- the first version issued a
+// second instruction for w1 and paid the L1 line-lookup cost of every row twice, which is what bounded
+// it (time did not change with the table size or dtype).  The loads of candidate c+1 are issued slot by
+// slot while candidate c's rows are consumed from the same registers (a rolling window of kIters loads
+// per lane, always full), so the warp never drains between candidates or between tiles.  The id / weight
+// lists of a warp tile are staged into the warp's own shared-memory buffers with cp.async.bulk (SASS
+// UBLKCP) on the warp's own mbarriers, double buffered.  Pooling (first-order sum, FM sums) is a fixed
+// per-lane order plus a fixed warp-shuffle tree: the same candidate gets bit-identical results at any
+// position, in any chunk, on any GPU, from any input format.
+//
+// Input formats.  (1) the reference's: ids int64 [n, F], wts float [n, F] (DC:97-108).  (2) compact
+// (kCompact): the first n_ctx fields of every candidate come from one shared list (kernel parameters),
+// the per-candidate list holds the remaining Fk = F - n_ctx ids as int64 or as uint32 ROW indices
+// (already hashed by the host packer), and weights only for the fields flagged in weighted_mask (the
+// others are 1.0) -- what ctr_predict_shared_async / ctr_predict_packed_async ship over the host link.
+//
+// Footprint: 256 threads x 64 registers and ~30 KB of shared memory per CTA, so that one CTA fits on an SM
+// NEXT TO the resident tower CTA (tower.cuh) and a chunk's gather runs under the previous chunk's tower.
 //
 // Roofline: HBM.  Algorithmic bytes per candidate (F=39: 13 dense + 26 sparse, fp32 table):
 // 468 (ids+wts) + 26*(64+4) (rows; the 13 dense-field rows stay in L1/L2) + 4 = 2240 B.
@@ -28,16 +40,22 @@
 
 namespace ctr {
 
-constexpr int kGatherTile = 32;        // candidates per staged tile
-constexpr int kGatherThreads = 256;    // 8 warps -> 4 candidates per warp per tile
-constexpr int kGatherRounds = 6;       // 8 fields per round -> F <= 48
+constexpr int kWarpTile = 4;           // candidates per warp tile
+constexpr int kGatherThreads = 256;    // 8 independent warps
+constexpr int kGatherWarps = kGatherThreads / 32;
 
 struct GatherParams {
-    const int64_t* ids;        // [n, F]
-    const float* wts;          // [n, F]
+    const void* ids;           // [n, Fk] int64 (id_bytes 8) or uint32 row indices (id_bytes 4)
+    const float* wts;          // [n, Wk]
     int64_t n;
-    int32_t F;
+    int32_t F;                 // fields of the model
+    int32_t Fk;                // id columns per candidate (F - n_ctx)
+    int32_t Wk;                // weight columns per candidate (popcount of weighted_mask over the per-candidate fields)
+    int32_t id_bytes;
+    int32_t n_ctx;             // leading fields taken from ctx_ids / ctx_wts (compact input only)
+    int32_t hashed;            // row = mix64(id) & (num_rows - 1); 0 for direct tables and for ids that already are rows
     int32_t bulk_ok;           // ids/wts base pointers are 16-byte aligned -> bulk copies allowed
+    uint64_t weighted_mask;    // bit f: per-candidate field f has a weight column (compact input only)
     const uint8_t* table;      // packed rows
     uint64_t num_rows;         // direct mode: bound; hashed mode: power of two
     float b0;
@@ -49,189 +67,246 @@ struct GatherParams {
     // row-sharded tables (rows striped over devices, row mod n_shards): peer base pointers
     int32_t n_shards;
     const uint8_t* shard_base[8];
+    int64_t ctx_ids[48];       // shared context (compact input): ids (or rows) and weights of fields 0 .. n_ctx-1
+    float ctx_wts[48];
 };
 
 template <int kTableDtype>
 struct RowLayout;
 template <>
-struct RowLayout<0> { static constexpr int shift = 7; static constexpr int w1_off = 64; };
+struct RowLayout<0> { static constexpr int shift = 7; static constexpr int w1_off = 64; static constexpr int lanes = 8; static constexpr int emb_lanes = 4; static constexpr int nv = 4; };
 template <>
-struct RowLayout<1> { static constexpr int shift = 6; static constexpr int w1_off = 32; };
+struct RowLayout<1> { static constexpr int shift = 6; static constexpr int w1_off = 32; static constexpr int lanes = 4; static constexpr int emb_lanes = 2; static constexpr int nv = 8; };
 
-__device__ __forceinline__ float4 ldg_nc_f4(const void* p) {
-    float4 v;
-    asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ uint2 ldg_nc_u2(const void* p) {
-    uint2 v;
-    asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ float ldg_nc_f1(const void* p) {
-    float v;
-    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+__device__ __forceinline__ uint4 ldg_nc_u4(const void* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
     return v;
 }
 
-// kTableDtype: 0 fp32 rows, 1 f16 rows.  kHashed: row = mix64(id) & (V-1).  kEmb: write X.
-// kLin: first-order sum.  kFM: DeepFM second-order term.  kSharded: rows striped over peers.
-#ifndef CTR_GATHER_MIN_CTAS
-#define CTR_GATHER_MIN_CTAS 4
-#endif
-template <int kTableDtype, bool kHashed, bool kEmb, bool kLin, bool kFM, bool kSharded>
-__global__ void __launch_bounds__(kGatherThreads, CTR_GATHER_MIN_CTAS)
-gather_pool_kernel(const GatherParams p) {
+// kTableDtype: 0 fp32 rows, 1 f16 rows.  kIters: load slots per lane and candidate (kIters * rows-per-load >= F).
+// kCompact: compact input (shared context / uint32 rows / sparse weights).  kEmb: write X.  kLin: first-order
+// sum.  kFM: DeepFM second-order term.
+template <int kTableDtype, int kIters, bool kCompact, bool kEmb, bool kLin, bool kFM>
+__global__ void __launch_bounds__(kGatherThreads, (kTableDtype == 0 && kIters > 10) ? 3 : 4)
+gather_pool_kernel(const __grid_constant__ GatherParams p) {
+    using RL = RowLayout<kTableDtype>;
+    constexpr int LPR = RL::lanes;              // lanes per row
+    constexpr int RPL = 32 / LPR;               // rows per load instruction
+    constexpr int NV = RL::nv;                  // embedding values per embedding lane
     extern __shared__ __align__(128) uint8_t gsm[];
-    const int F = p.F;
-    const uint32_t ids_bytes = kGatherTile * F * 8, wts_bytes = kGatherTile * F * 4;
-    // [ids buf0 | ids buf1 | wts buf0 | wts buf1]; pointer arithmetic (not arrays) keeps this out of local memory
-    auto ids_buf = [&](int buf) { return reinterpret_cast<int64_t*>(gsm + buf * ids_bytes); };
-    auto wts_buf = [&](int buf) { return reinterpret_cast<float*>(gsm + 2 * ids_bytes + buf * wts_bytes); };
-    __shared__ __align__(8) uint64_t full_bar[2];
+    __shared__ __align__(8) uint64_t full_bar[kGatherWarps][2];
+    __shared__ int64_t s_ctx_id[kCompact ? 48 : 1];
+    __shared__ float s_ctx_wt[kCompact ? 48 : 1];
 
+    const int F = p.F, Fk = p.Fk, Wk = p.Wk;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, q = lane & 3;
-    const int64_t n_tiles = (p.n + kGatherTile - 1) / kGatherTile;
+    const int g = lane / LPR, q = lane % LPR;
+    const uint32_t ids_bytes = (uint32_t)(kWarpTile * Fk * p.id_bytes), wts_bytes = (uint32_t)(kWarpTile * Wk * 4);   // multiples of 16
+    const uint32_t buf_bytes = ids_bytes + wts_bytes;
+    uint8_t* const wbase = gsm + (size_t)warp * 2 * buf_bytes;
+    const int64_t n_tiles = (p.n + kWarpTile - 1) / kWarpTile;
 
-    if (tid == 0) {
-        mbar_init(&full_bar[0], 1);
-        mbar_init(&full_bar[1], 1);
+    if (kCompact) {
+        for (int f = tid; f < p.n_ctx; f += kGatherThreads) { s_ctx_id[f] = p.ctx_ids[f]; s_ctx_wt[f] = p.ctx_wts[f]; }
+    }
+    if (lane == 0) {
+        mbar_init(&full_bar[warp][0], 1);
+        mbar_init(&full_bar[warp][1], 1);
         mbar_fence_init();
     }
-    __syncthreads();
+    __syncthreads();                        // the only block-wide barrier: from here on every warp is on its own
 
-    // Stage the id / weight lists of one tile.  Full, aligned tiles: one elected thread
-    // issues two bulk copies that complete on full_bar[buf].  The ragged last tile (or
-    // unaligned caller pointers) falls back to ordinary loads by the whole CTA.
-    auto tile_is_bulk = [&](int64_t tile) { return p.bulk_ok && (tile + 1) * kGatherTile <= p.n; };
-    auto stage = [&](int64_t tile, int buf) {
-        const int64_t c0 = tile * kGatherTile;
+    // Stage the id / weight lists of one warp tile into this warp's buffer `b`.  Full, aligned tiles: one lane
+    // issues two bulk copies that complete on the warp's mbarrier.  The ragged last tile (or unaligned caller
+    // pointers) is copied with ordinary loads by the warp.
+    const uint8_t* const gids = static_cast<const uint8_t*>(p.ids);
+    auto tile_is_bulk = [&](int64_t tile) { return p.bulk_ok && (tile + 1) * kWarpTile <= p.n; };
+    auto stage = [&](int64_t tile, int b) {
+        const int64_t c0 = tile * kWarpTile;
+        uint8_t* dst = wbase + b * buf_bytes;
+        __syncwarp();                                          // every lane is done reading what `b` held before
         if (tile_is_bulk(tile)) {
-            if (tid == 0) {
+            if (lane == 0) {
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_expect_tx(&full_bar[buf], ids_bytes + wts_bytes);
-                bulk_g2s(ids_buf(buf), p.ids + c0 * F, ids_bytes, &full_bar[buf]);
-                bulk_g2s(wts_buf(buf), p.wts + c0 * F, wts_bytes, &full_bar[buf]);
+                mbar_expect_tx(&full_bar[warp][b], buf_bytes);
+                bulk_g2s(dst, gids + (size_t)c0 * Fk * p.id_bytes, ids_bytes, &full_bar[warp][b]);
+                if (wts_bytes) bulk_g2s(dst + ids_bytes, p.wts + (size_t)c0 * Wk, wts_bytes, &full_bar[warp][b]);
             }
         } else {
-            const int64_t cnt = min((int64_t)kGatherTile, p.n - c0) * F;
-            int64_t* di = ids_buf(buf);
-            float* dw = wts_buf(buf);
-            for (int64_t i = tid; i < cnt; i += kGatherThreads) {
-                di[i] = p.ids[c0 * F + i];
-                dw[i] = p.wts[c0 * F + i];
+            const int cnt = (int)min((int64_t)kWarpTile, p.n - c0);
+            const uint32_t* si = reinterpret_cast<const uint32_t*>(gids + (size_t)c0 * Fk * p.id_bytes);
+            uint32_t* di = reinterpret_cast<uint32_t*>(dst);
+            for (int i = lane; i < cnt * Fk * (p.id_bytes >> 2); i += 32) di[i] = si[i];
+            float* dw = reinterpret_cast<float*>(dst + ids_bytes);
+            for (int i = lane; i < cnt * Wk; i += 32) dw[i] = p.wts[(size_t)c0 * Wk + i];
+            __syncwarp();
+        }
+    };
+
+    // id and weight of (candidate c of the tile in buffer `buf`, field f)
+    auto fetch_id = [&](const uint8_t* buf, int c, int f) -> uint64_t {
+        if (kCompact) {
+            if (f < p.n_ctx) return (uint64_t)s_ctx_id[f];
+            const int col = c * Fk + (f - p.n_ctx);
+            return p.id_bytes == 4 ? (uint64_t)reinterpret_cast<const uint32_t*>(buf)[col] : (uint64_t)reinterpret_cast<const int64_t*>(buf)[col];
+        }
+        return (uint64_t)reinterpret_cast<const int64_t*>(buf)[c * F + f];
+    };
+    auto fetch_wt = [&](const uint8_t* buf, int c, int f) -> float {
+        const float* swt = reinterpret_cast<const float*>(buf + ids_bytes);
+        if (kCompact) {
+            if (f < p.n_ctx) return s_ctx_wt[f];
+            const uint64_t m = p.weighted_mask >> p.n_ctx;
+            const int j = f - p.n_ctx;
+            if (!((m >> j) & 1ull)) return 1.0f;
+            return swt[c * Wk + __popcll(m & ((1ull << j) - 1ull))];
+        }
+        return swt[c * F + f];
+    };
+
+    // the rolling window of row loads: slot j holds the 16 bytes this lane fetched of row (field j*RPL + g)
+    uint4 ev[kIters];
+    const bool emb_lane = q < RL::emb_lanes, w1_lane = q == RL::emb_lanes;
+    const bool load_lane = (emb_lane && (kEmb || kFM)) || (w1_lane && kLin);
+
+    // issue the load of slot j for candidate c of the tile in `buf`; returns 1 when the id was out of range
+    auto issue = [&](int j, const uint8_t* buf, int c) -> uint32_t {
+        const int f = j * RPL + g;
+        ev[j] = make_uint4(0u, 0u, 0u, 0u);
+        uint32_t bad = 0;
+        if (j * RPL < F && f < F) {
+            const uint64_t id = fetch_id(buf, c, f);
+            uint64_t row;
+            if (p.hashed) {
+                row = mix64(id) & (p.num_rows - 1);
+            } else {
+                row = id;
+                if (row >= p.num_rows) { row = 0; bad = 1; *p.error_flag = 1; }
+            }
+            const uint8_t* base = p.table;
+            if (p.n_shards > 1) {
+                const uint32_t owner = (uint32_t)(row % (uint32_t)p.n_shards);
+                row = row / (uint32_t)p.n_shards;
+                base = p.shard_base[owner];
+            }
+            if (load_lane) ev[j] = ldg_nc_u4(base + (row << RL::shift) + q * 16);
+        }
+        return bad;
+    };
+
+    // per-candidate accumulators (of the candidate being consumed)
+    float lin, s2, s1[NV];
+    auto reset_acc = [&]() {
+        lin = 0.f; s2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) s1[k] = 0.f;
+    };
+    // consume slot j of candidate (global index b, candidate c of the tile in `buf`); `bad`: its id was out of range
+    auto consume = [&](int j, const uint8_t* buf, int c, int64_t b, uint32_t bad) {
+        const int f = j * RPL + g;
+        if (j * RPL < F) {
+            float wt = (f < F && !bad) ? fetch_wt(buf, c, f) : 0.f;
+            if (emb_lane && (kEmb || kFM)) {
+                float x[NV];
+                if (kTableDtype == 0) {
+                    x[0] = __uint_as_float(ev[j].x) * wt; x[1] = __uint_as_float(ev[j].y) * wt;
+                    x[2] = __uint_as_float(ev[j].z) * wt; x[3] = __uint_as_float(ev[j].w) * wt;
+                } else {
+                    const uint32_t w4[4] = {ev[j].x, ev[j].y, ev[j].z, ev[j].w};
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&w4[k]));
+                        x[2 * k] = a.x * wt; x[2 * k + 1] = a.y * wt;
+                    }
+                }
+                if (kFM) {
+#pragma unroll
+                    for (int k = 0; k < NV; ++k) { s1[k] += x[k]; s2 = fmaf(x[k], x[k], s2); }
+                }
+                if (kEmb && f < F) {
+                    uint32_t o[NV / 2];
+#pragma unroll
+                    for (int k = 0; k < NV / 2; ++k) o[k] = pack_half2_sat(x[2 * k], x[2 * k + 1]);
+                    __half* dst = p.X + b * p.ldx + f * kEmbDim + q * NV;
+                    if (NV == 4) *reinterpret_cast<uint2*>(dst) = make_uint2(o[0], o[1]);
+                    else *reinterpret_cast<uint4*>(dst) = make_uint4(o[0], o[1], o[NV / 2 - 2], o[NV / 2 - 1]);
+                }
+            } else if (kLin && w1_lane) {
+                lin = fmaf(__uint_as_float(ev[j].x), wt, lin);
+            }
+        }
+    };
+    // after the last slot of a candidate: pool over the warp and write lin (+FM) / the LR score
+    auto finish = [&](int64_t b) {
+        if (kLin || kFM) {
+            float acc = lin;                                  // only the w1 lanes hold first-order terms
+            if (kFM) {
+                // field sums per embedding coordinate: reduce over the lane groups (same q, different g)
+#pragma unroll
+                for (int off = LPR; off <= 16; off <<= 1) {
+#pragma unroll
+                    for (int k = 0; k < NV; ++k) s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], off);
+                }
+                float sq = 0.f;
+#pragma unroll
+                for (int k = 0; k < NV; ++k) sq = fmaf(s1[k], s1[k], sq);
+                acc += (g == 0 && emb_lane ? 0.5f * sq : 0.f) - 0.5f * s2;
+            }
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+            if (lane == 0) {
+                const float z = acc + p.b0;
+                if (p.wide) p.wide[b] = z;
+                if (p.scores) p.scores[b] = sigmoidf_fast(z);
             }
         }
     };
 
-    uint32_t phase_bits = 0;                               // bit b = parity to wait for on full_bar[b]
-    int64_t tile = blockIdx.x;
-    if (tile < n_tiles) stage(tile, 0);
-    __syncthreads();
+    const int64_t tile_stride = (int64_t)gridDim.x * kGatherWarps;
+    int64_t tile = (int64_t)blockIdx.x * kGatherWarps + warp;
+    if (tile >= n_tiles) return;
+    stage(tile, 0);
 
-    for (int it = 0; tile < n_tiles; tile += gridDim.x, ++it) {
-        const int buf = it & 1;
-        const int64_t next = tile + gridDim.x;
-        if (next < n_tiles) stage(next, buf ^ 1);          // buf^1 was released by the barrier below
+    uint32_t phase_bits = 0;                               // bit b = parity to wait for on full_bar[warp][b]
+    bool have_prev = false;                                // a candidate's loads are in flight in ev[]
+    const uint8_t* prev_buf = nullptr;
+    int prev_c = 0;
+    int64_t prev_b = 0;
+    uint32_t prev_bad = 0;                                 // bit j: slot j of the candidate in flight had a bad id (per lane)
+    for (int it = 0; tile < n_tiles; tile += tile_stride, ++it) {
+        const int bsel = it & 1;
+        const uint8_t* buf = wbase + bsel * buf_bytes;
         if (tile_is_bulk(tile)) {
-            mbar_wait(&full_bar[buf], (phase_bits >> buf) & 1u);
-            phase_bits ^= 1u << buf;
+            mbar_wait(&full_bar[warp][bsel], (phase_bits >> bsel) & 1u);
+            phase_bits ^= 1u << bsel;
         }
-        const int64_t c0 = tile * kGatherTile;
-        const int n_here = (int)min((int64_t)kGatherTile, p.n - c0);
-
-        for (int c = warp; c < n_here; c += kGatherThreads / 32) {
-            const int64_t b = c0 + c;
-            const int64_t* sid = ids_buf(buf) + c * F;
-            const float* swt = wts_buf(buf) + c * F;
-
-            float4 ev[kGatherRounds];
-            float wv[kGatherRounds], w1v[kGatherRounds];
+        const int64_t c0 = tile * kWarpTile;
+        const int n_here = (int)min((int64_t)kWarpTile, p.n - c0);
+        for (int c = 0; c < n_here; ++c) {
+            uint32_t bad = 0;
+            if (have_prev) {
+                reset_acc();
 #pragma unroll
-            for (int r = 0; r < kGatherRounds; ++r) {
-                ev[r] = make_float4(0.f, 0.f, 0.f, 0.f);
-                wv[r] = 0.f;
-                w1v[r] = 0.f;
-                const int f = r * 8 + g;
-                if (r * 8 < F && f < F) {
-                    const int64_t id = sid[f];
-                    wv[r] = swt[f];
-                    uint64_t row;
-                    if (kHashed) {
-                        row = mix64((uint64_t)id) & (p.num_rows - 1);
-                    } else {
-                        row = (uint64_t)id;
-                        if (row >= p.num_rows) { row = 0; wv[r] = 0.f; *p.error_flag = 1; }
-                    }
-                    const uint8_t* base = p.table;
-                    if (kSharded) {
-                        const uint32_t owner = (uint32_t)(row % (uint32_t)p.n_shards);
-                        row = row / (uint32_t)p.n_shards;
-                        base = p.shard_base[owner];
-                    }
-                    const uint8_t* rp = base + (row << RowLayout<kTableDtype>::shift);
-                    if (kEmb || kFM) {
-                        if (kTableDtype == 0) {
-                            ev[r] = ldg_nc_f4(rp + q * 16);
-                        } else {
-                            const uint2 h = ldg_nc_u2(rp + q * 8);
-                            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&h.x));
-                            const float2 c2 = __half22float2(*reinterpret_cast<const __half2*>(&h.y));
-                            ev[r] = make_float4(a.x, a.y, c2.x, c2.y);
-                        }
-                    }
-                    if (kLin && q == 0) w1v[r] = ldg_nc_f1(rp + RowLayout<kTableDtype>::w1_off);
+                for (int j = 0; j < kIters; ++j) {
+                    consume(j, prev_buf, prev_c, prev_b, (prev_bad >> j) & 1u);
+                    bad |= issue(j, buf, c) << j;
                 }
+                finish(prev_b);
+            } else {
+#pragma unroll
+                for (int j = 0; j < kIters; ++j) bad |= issue(j, buf, c) << j;
             }
-
-            float lin = 0.f, s2 = 0.f;
-            float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int r = 0; r < kGatherRounds; ++r) {
-                const int f = r * 8 + g;
-                if (r * 8 < F) {
-                    const float wt = wv[r];
-                    const float4 x = make_float4(ev[r].x * wt, ev[r].y * wt, ev[r].z * wt, ev[r].w * wt);
-                    if (kLin) lin = fmaf(w1v[r], wt, lin);
-                    if (kFM) {
-                        s1.x += x.x; s1.y += x.y; s1.z += x.z; s1.w += x.w;
-                        s2 = fmaf(x.x, x.x, s2); s2 = fmaf(x.y, x.y, s2); s2 = fmaf(x.z, x.z, s2); s2 = fmaf(x.w, x.w, s2);
-                    }
-                    if (kEmb && f < F) {
-                        const __half2 h01 = __floats2half2_rn(x.x, x.y), h23 = __floats2half2_rn(x.z, x.w);
-                        uint2 o;
-                        o.x = *reinterpret_cast<const uint32_t*>(&h01);
-                        o.y = *reinterpret_cast<const uint32_t*>(&h23);
-                        *reinterpret_cast<uint2*>(p.X + b * p.ldx + f * kEmbDim + q * 4) = o;
-                    }
-                }
-            }
-
-            if (kLin || kFM) {
-                float acc = lin;                              // only q==0 lanes hold first-order terms
-                if (kFM) {
-                    // field sums per embedding coordinate: reduce over the 8 lane groups
-#pragma unroll
-                    for (int off = 4; off <= 16; off <<= 1) {
-                        s1.x += __shfl_xor_sync(0xffffffffu, s1.x, off);
-                        s1.y += __shfl_xor_sync(0xffffffffu, s1.y, off);
-                        s1.z += __shfl_xor_sync(0xffffffffu, s1.z, off);
-                        s1.w += __shfl_xor_sync(0xffffffffu, s1.w, off);
-                    }
-                    const float sq = s1.x * s1.x + s1.y * s1.y + s1.z * s1.z + s1.w * s1.w;
-                    acc += (g == 0 ? 0.5f * sq : 0.f) - 0.5f * s2;
-                }
-#pragma unroll
-                for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-                if (lane == 0) {
-                    const float z = acc + p.b0;
-                    if (p.wide) p.wide[b] = z;
-                    if (p.scores) p.scores[b] = sigmoidf_fast(z);
-                }
-            }
+            have_prev = true; prev_buf = buf; prev_c = c; prev_b = c0 + c; prev_bad = bad;
+            // the previous tile's buffer has been read for the last time: stage the next tile into it
+            if (c == 0 && tile + tile_stride < n_tiles) stage(tile + tile_stride, bsel ^ 1);
         }
-        __syncthreads();   // every warp is done with buf before it is staged again
+    }
+    if (have_prev) {
+        reset_acc();
+#pragma unroll
+        for (int j = 0; j < kIters; ++j) consume(j, prev_buf, prev_c, prev_b, (prev_bad >> j) & 1u);
+        finish(prev_b);
     }
 }
 
@@ -282,22 +357,6 @@ __global__ void pack_table_kernel(uint8_t* table, uint64_t dst_row0, const float
             *reinterpret_cast<uint2*>(rp + q * 8) = o;
         }
         if (q == 0) *reinterpret_cast<float*>(rp + RowLayout<kTableDtype>::w1_off) = w1[r];
-    }
-}
-
-// Shared-context requests: the reference replicates every user / context
-// field for every candidate (DCNClient.java:61-63, :70-72).  Here the context list crosses the host
-// link once; this kernel rebuilds the reference layout [n, F] in HBM: field f < n_ctx of every
-// candidate comes from the shared list, the rest from the candidate's own compact list.
-__global__ void expand_context_kernel(const int64_t* ctx_ids, const float* ctx_wts, int n_ctx, const int64_t* cand_ids,
-                                      const float* cand_wts, int64_t n, int F, int64_t* ids_out, float* wts_out) {
-    const int Fk = F - n_ctx;
-    const int64_t total = n * F;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t b = i / F;
-        const int f = (int)(i - b * F);
-        ids_out[i] = f < n_ctx ? ctx_ids[f] : cand_ids[b * Fk + (f - n_ctx)];
-        wts_out[i] = f < n_ctx ? ctx_wts[f] : cand_wts[b * Fk + (f - n_ctx)];
     }
 }
 

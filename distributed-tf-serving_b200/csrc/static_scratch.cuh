@@ -67,6 +67,10 @@ extern "C" int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, 
     unsigned char* base = nullptr;
     int32_t rc = static_scratch_for_device(dm.dev, &base);      // first call on this GPU resolves the address
     if (rc != CTR_OK) return rc;
+    // Host threads that call in at the same time must not interleave their enqueues (one call's clearing
+    // memset would land between another call's gather and tower): the whole enqueue -- and, on the engine's
+    // own stream, the wait and the flag read as well -- runs under the device's mutex, like ctr_score_device.
+    std::lock_guard<std::mutex> lk(dc.dev_mu);
     CUDA_TRY(cudaSetDevice(dm.dev));
     cudaStream_t user = reinterpret_cast<cudaStream_t>(stream);
     cudaStream_t st = user ? user : dc.main_stream;
@@ -97,8 +101,8 @@ extern "C" int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, 
     }
     CUDA_TRY(cudaMemsetAsync(s.d_err, 0, sizeof(int32_t), st));
 
-    rc = score_chunk(e, dc, s, static_cast<const int64_t*>(d_ids), static_cast<const float*>(d_wts), (int)n_cand,
-                     static_cast<float*>(d_scores));
+    s.owns_buffers = false;                   // bring-up profiling (which allocates) is refused for this slot
+    rc = score_chunk(e, dc, s, reference_view(d_ids, static_cast<const float*>(d_wts), m.F), (int)n_cand, static_cast<float*>(d_scores));
     s.stream = nullptr;                       // nothing of this slot is owned: keep free_slot-style cleanup away from it
     if (rc != CTR_OK) return rc;
     if (!user) {

@@ -93,6 +93,12 @@ struct ChainParams {
     float* scores;             // [M]: sigmoid(dot + ...) after a dot layer, or nullptr
     float* extra_out;          // [M]: raw dot after a dot layer, or nullptr
     long long* prof;           // bring-up instrumentation (nullptr in production)
+    // The pair scratch is ONE allocation per device, shared by every stream: a CTA pair takes a free slice from
+    // this bitmap when it starts and gives it back when it leaves (at most num_sms / 2 pairs are ever resident,
+    // one per TPC, whatever the number of streams).  nullptr: slice = pair index of this launch (the caller
+    // guarantees that no other launch uses the same scratch at the same time).
+    unsigned long long* slice_bitmap;
+    int32_t n_slices;
 };
 
 struct ChainMaps {
@@ -212,17 +218,23 @@ __device__ __forceinline__ void epilogue_tile(const ChainParams& p, const ChainL
             const int step = L.out_global ? 8 : kBM * 8;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                __half2 h[4];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) h[e] = __floats2half2_rn(v[8 * j + 2 * e], v[8 * j + 2 * e + 1]);
-                *reinterpret_cast<uint4*>(o + j * step) = *reinterpret_cast<const uint4*>(h);
+                uint4 h;                                             // saturating: a layer output beyond the half range is clamped, never inf
+                h.x = pack_half2_sat(v[8 * j + 0], v[8 * j + 1]); h.y = pack_half2_sat(v[8 * j + 2], v[8 * j + 3]);
+                h.z = pack_half2_sat(v[8 * j + 4], v[8 * j + 5]); h.w = pack_half2_sat(v[8 * j + 6], v[8 * j + 7]);
+                *reinterpret_cast<uint4*>(o + j * step) = h;
             }
         }
     }
 }
 
+// Register budget.  The kernel is launched with 128 registers per thread (12 warps x 32 x 128 = 48 K of the SM's
+// 64 K), then the four control warps shrink to 48 and the eight epilogue warps grow to 168 (setmaxnreg, one
+// instruction per warp group): 4 x 32 x 48 + 8 x 32 x 168 = 48 K.  The 16 K registers and ~30 KB of shared
+// memory this leaves on every SM are what one 256-thread CTA of the gather kernel (gather.cuh, 64 registers)
+// needs, so the next chunk's gather runs on the same SMs UNDER this kernel instead of in front of it.
+constexpr int kTowerLaunchRegThreads = 512;    // __launch_bounds__ max-threads that makes ptxas allocate 128 registers
 template <int BN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kGemmThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kTowerLaunchRegThreads, 1)
 tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant__ ChainParams p) {
     using Cfg = ChainCfg<BN>;
     constexpr int kStages = Cfg::kStages;
@@ -239,6 +251,7 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     uint64_t* layer_done = bars + 2 * kStages + 4; // [2] in each CTA, one per interleaved tile: epilogue (layer l stored) -> producer (layer l+1 A loads)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 6);
     __shared__ float dot_part[2 * kBM];            // high-column-half partial dots, double-buffered
+    __shared__ int slice_sh;                       // this pair's slice of the activation scratch
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = cluster_ctarank();
@@ -261,11 +274,30 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         tmem_alloc_pair(tmem_slot, Cfg::kTmemCols);
         tmem_relinquish_pair();
     }
+    if (warp == 3 && lane == 0 && leader) {
+        // take a free scratch slice (the search starts at a different bit in every pair, so the pairs of a
+        // launch rarely collide), publish it in both CTAs; the cluster barrier below makes it visible
+        int slice = pair_id;
+        if (p.slice_bitmap) {
+            slice = -1;
+            const uint64_t t0 = globaltimer_ns();
+            for (int probe = pair_id % p.n_slices; slice < 0; probe = probe + 1 == p.n_slices ? 0 : probe + 1) {
+                const unsigned long long bit = 1ull << (probe & 63);
+                if (!(atomicOr(&p.slice_bitmap[probe >> 6], bit) & bit)) slice = probe;
+                else if (probe == 0 && globaltimer_ns() - t0 > 2000000000ull) __trap();   // leaked slices: an earlier launch died
+            }
+        }
+        slice_sh = slice;
+        asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(map_to_cta(smem_u32(&slice_sh), 1)), "r"(slice) : "memory");
+    }
     tc_fence_before();
     cluster_sync_all();                              // barriers of both CTAs are initialised before anyone signals them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    const int slice = slice_sh;
 
+    if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 48;");       // one instruction for the whole warp group
     if (warp == 0) {
         // ===================== TMA producer (both CTAs) =====================
         // The whole warp walks the loop (so addresses and coordinates stay in uniform registers) and one
@@ -280,7 +312,7 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                     const ChainLayer& L = p.layer[l];
                     const int t = t0 + sub * n_pairs;
                     const int a_row = t * 2 * kBM + (int)rank * kBM;          // row-major A: candidate rows
-                    const int a_tile = (pair_id * 2 + sub) * 2 + (int)rank;   // tile-major A: this CTA's scratch tile
+                    const int a_tile = (slice * 2 + sub) * 2 + (int)rank;     // tile-major A: this CTA's scratch tile
                     const int tiles_n = (L.N + BN - 1) / BN, k_blocks = L.K / kBK;
                     for (int nt = 0; nt < tiles_n; ++nt) {
                         // the last tile of a layer may be 128 wide: each CTA then feeds the first 64 rows of its box
@@ -376,7 +408,9 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
                 p.prof[(blockIdx.x + 1) * 8 + 4] = (long long)(globaltimer_ns() - ns0);     // peer's slot: wall time of the same loop
             }
         }
-    } else if (warp >= 4) {
+    }
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 168;");
         // ===================== epilogue (8 warps, both CTAs, own 128 rows) =====================
         // A warp may only touch the TMEM lanes of its sub-partition (warp % 4); two warps share a
         // sub-partition and split the tile's columns in halves.
@@ -391,7 +425,7 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             for (int st = 0; st < n_sub; ++st) {                                     // the two interleaved tiles of this pair
                 const int t = t0 + st * n_pairs;
                 const int grow = t * 2 * kBM + (int)rank * kBM + sub * 32 + lane;        // this thread's candidate row
-                const int stile = (pair_id * 2 + st) * 2 + (int)rank;                     // this CTA's 128-row scratch tile
+                const int stile = (slice * 2 + st) * 2 + (int)rank;                       // this CTA's 128-row scratch tile
                 const ChainLayer& L = p.layer[l];
                 const int tiles_n = (L.N + BN - 1) / BN;
                 const bool dot_epi = L.epi == EPI_HEAD || L.epi == EPI_CROSS_DOT;
@@ -451,6 +485,10 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     if (warp == 2) {
         tc_fence_after();
         tmem_dealloc_pair(tmem_base, Cfg::kTmemCols);
+    }
+    if (warp == 3 && lane == 0 && leader && p.slice_bitmap) {     // every access of this pair to its slice is behind the barrier above
+        __threadfence();
+        atomicAnd(&p.slice_bitmap[slice >> 6], ~(1ull << (slice & 63)));
     }
 }
 

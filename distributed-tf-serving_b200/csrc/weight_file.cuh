@@ -5,6 +5,7 @@ namespace {
 constexpr char kMagic[8] = {'C', 'T', 'R', 'W', '0', '0', '0', '1'};
 constexpr size_t kHeaderBytes = 128;
 constexpr uint64_t kTagE = 1, kTagW1 = 2;
+constexpr int kMaxHiddenWidth = 16384;
 
 struct ModelDesc {
     int32_t kind = 0, F = 0, K = 0, id_mode = 0, table_dtype = 0, table_mode = 0, n_hidden = 0;
@@ -48,12 +49,15 @@ int32_t read_weight_file(const char* path, HostWeights* hw) {
     if (m.kind < 0 || m.kind > 3) return bad("unknown model kind");
     if (m.K != kEmbDim) return bad("embedding dim must be 16");
     if (m.F < 1 || m.F > CTR_MAX_FIELDS) return bad("field count out of range (1..48)");
-    if (m.V < 1) return bad("row count must be positive");
+    if (m.V < 1 || m.V > ((int64_t)1 << 40)) return bad("row count out of range (1 .. 2^40)");
+    if (m.id_mode != CTR_ID_DIRECT && m.id_mode != CTR_ID_HASHED) return bad("unknown id mode");
+    if (m.table_dtype != CTR_TABLE_FP32 && m.table_dtype != CTR_TABLE_F16) return bad("unknown table dtype");
+    if (m.table_mode != 0 && m.table_mode != 1) return bad("unknown table mode (0 = raw rows in the file, 1 = procedural)");
     if (m.id_mode == CTR_ID_HASHED && (m.V & (m.V - 1))) return bad("hashed tables need a power-of-two row count");
     if (m.n_hidden < 0 || m.n_hidden > CTR_MAX_HIDDEN) return bad("too many hidden layers");
     if (m.kind != CTR_MODEL_LR && m.n_hidden < 1) return bad("tower needs at least one hidden layer");
     for (int i = 0; i < m.n_hidden; ++i)
-        if (m.hidden[i] < 8 || m.hidden[i] % 8) return bad("hidden sizes must be positive multiples of 8");
+        if (m.hidden[i] < 8 || m.hidden[i] % 8 || m.hidden[i] > kMaxHiddenWidth) return bad("hidden sizes must be multiples of 8 in 8..16384");
     if (m.kind != CTR_MODEL_DCN_V2) m.n_cross = 0;
     if (m.n_cross < 0 || m.n_cross > 4) return bad("cross layer count out of range (0..4)");
     if (m.kind == CTR_MODEL_DCN_V2 && m.n_cross < 1) return bad("DCN-v2 needs at least one cross layer");
@@ -75,7 +79,18 @@ int32_t read_weight_file(const char* path, HostWeights* hw) {
         hw->off_wout = n; n += (size_t)m.head_in();
         hw->off_bout = n; n += 1;
     }
-    hw->blob.resize(n);
+    // the header decides how many floats follow: check it against the file before allocating for it
+    const long data_pos = ftell(f);
+    if (data_pos < 0 || fseek(f, 0, SEEK_END) != 0) return bad("cannot seek");
+    const long end_pos = ftell(f);
+    if (end_pos < data_pos || fseek(f, data_pos, SEEK_SET) != 0) return bad("cannot seek");
+    if ((uint64_t)(end_pos - data_pos) != (uint64_t)n * sizeof(float))
+        return bad(end_pos - data_pos < (long)(n * sizeof(float)) ? "truncated tensor data" : "trailing bytes after the last tensor");
+    try {
+        hw->blob.resize(n);
+    } catch (const std::exception&) {
+        return bad("not enough host memory for the tensors the header describes");
+    }
     size_t got = fread(hw->blob.data(), sizeof(float), n, f);
     unsigned char extra;
     bool trailing = fread(&extra, 1, 1, f) == 1;

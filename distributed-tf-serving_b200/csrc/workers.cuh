@@ -34,38 +34,25 @@ void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t st
 
 // sendRequest (DC:91-115) for one shard: stage -> H2D -> kernels -> D2H -> hand back.
 void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
-    const ModelDesc& m = e->m;
     auto body = [&]() -> int32_t {
         CUDA_TRY(cudaSetDevice(s.dev));
-        const int Fk = m.F - t.n_ctx;                          // per-candidate fields actually shipped
-        const size_t ib = (size_t)t.n * Fk * sizeof(int64_t), wb = (size_t)t.n * Fk * sizeof(float), sb = (size_t)t.n * sizeof(float);
+        const InputView& in = t.in;
+        const size_t ib = in.ids_bytes(t.n), wb = in.wts_bytes(t.n), sb = (size_t)t.n * sizeof(float);
         // The feature packer: caller buffers that came from ctr_alloc_pinned are DMA'd in place;
         // pageable ones (a Java heap array, a numpy array) are packed into this slot's pinned slab.
-        const int64_t* src_ids = t.ids;
-        const float* src_wts = t.wts;
-        if (!is_pinned(e, t.ids, ib)) { memcpy(s.h_ids, t.ids, ib); src_ids = s.h_ids; }
-        if (!is_pinned(e, t.wts, wb)) { memcpy(s.h_wts, t.wts, wb); src_wts = s.h_wts; }
+        const void* src_ids = in.ids;
+        const float* src_wts = in.wts;
+        if (!is_pinned(e, in.ids, ib)) { memcpy(s.h_ids, in.ids, ib); src_ids = s.h_ids; }
+        if (wb && !is_pinned(e, in.wts, wb)) { memcpy(s.h_wts, in.wts, wb); src_wts = s.h_wts; }
         const bool out_pinned = is_pinned(e, t.scores, sb);
         float* dst_scores = out_pinned ? t.scores : s.h_scores;
-        if (t.n_ctx == 0) {
-            CUDA_TRY(cudaMemcpyAsync(s.d_ids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
-            CUDA_TRY(cudaMemcpyAsync(s.d_wts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
-        } else {
-            // shared context: ship the per-candidate fields once and the context list once, rebuild the
-            // reference layout [n, F] on the device (HBM bandwidth is cheap, the host link is not)
-            CUDA_TRY(cudaMemcpyAsync(s.d_cids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
-            CUDA_TRY(cudaMemcpyAsync(s.d_cwts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
-            int64_t* d_ctx_ids = s.d_cids + (size_t)s.cap * m.F;
-            float* d_ctx_wts = s.d_cwts + (size_t)s.cap * m.F;
-            CUDA_TRY(cudaMemcpyAsync(d_ctx_ids, t.ctx_ids, (size_t)t.n_ctx * sizeof(int64_t), cudaMemcpyHostToDevice, s.stream));
-            CUDA_TRY(cudaMemcpyAsync(d_ctx_wts, t.ctx_wts, (size_t)t.n_ctx * sizeof(float), cudaMemcpyHostToDevice, s.stream));
-            const int64_t total = t.n * m.F;
-            expand_context_kernel<<<(int)std::min<int64_t>((total + 255) / 256, dc.model.num_sms * 16), 256, 0, s.stream>>>(
-                d_ctx_ids, d_ctx_wts, t.n_ctx, s.d_cids, s.d_cwts, t.n, m.F, s.d_ids, s.d_wts);
-            CUDA_TRY(cudaGetLastError());
-            e->launches.fetch_add(1, std::memory_order_relaxed);
-        }
-        int32_t rc = score_on_slot(e, dc, s, s.d_ids, s.d_wts, t.n, s.d_scores);
+        // Whatever the layout (reference, shared context, packed rows), the lists cross the host link as they
+        // are and the gather kernel reads them as they are: the shared context rides in the kernel parameters.
+        CUDA_TRY(cudaMemcpyAsync(s.d_ids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
+        if (wb) CUDA_TRY(cudaMemcpyAsync(s.d_wts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
+        InputView dv = in;
+        dv.ids = s.d_ids; dv.wts = s.d_wts;
+        int32_t rc = score_on_slot(e, dc, s, dv, t.n, s.d_scores);
         if (rc != CTR_OK) return rc;
         const float* d_result = s.d_scores;
         if (t.sort) {                                          // DC:195 before the scores leave the device
@@ -116,15 +103,22 @@ void stop_workers(ctr_engine* e) {
         if (dc.threads.empty()) continue;
         {
             std::lock_guard<std::mutex> lk(dc.q_mu);
-            Task t; t.stop = true; t.ids = nullptr; t.wts = nullptr; t.n = 0; t.scores = nullptr;
+            Task t; t.stop = true;
             dc.queue.push_back(t);
             dc.queued.fetch_add(1, std::memory_order_release);
         }
         dc.q_cv.notify_all();
         for (auto& th : dc.threads) th.join();
         dc.threads.clear();
-        dc.queue.clear();
-        dc.queued.store(0);
+        // a request that raced the stop marker must still complete, or its ctr_wait(-1) would never return
+        std::deque<Task> left;
+        {
+            std::lock_guard<std::mutex> lk(dc.q_mu);
+            left.swap(dc.queue);
+            dc.queued.store(0);
+        }
+        for (Task& t : left)
+            if (!t.stop && t.req) complete_shard(e, t.req, CTR_ERR_STATE, "engine stopped (weights reloaded or engine destroyed) before the request ran");
     }
 }
 
@@ -135,6 +129,7 @@ void free_device_state(ctr_engine* e) {
         for (auto& s : dc.dev_slots) free_slot(*s);
         dc.worker_slots.clear();
         dc.dev_slots.clear();
+        free_pair_scratch(dc);
         if (dc.model.dev >= 0) free_model(dc.model);
         if (dc.sort_cap) {
             cudaFree(dc.srt_scores);

@@ -62,7 +62,10 @@ typedef struct ctr_config {
     int32_t struct_size;          /* sizeof(ctr_config), for ABI checking */
     int32_t n_devices;            /* number of GPUs this engine fans out to (hostsList.size(), DC:38) */
     int32_t device_ids[CTR_MAX_DEVICES];
-    int32_t max_candidates;       /* capacity of ONE request (candidateNum, DC:29) */
+    int32_t max_candidates;       /* capacity of ONE shard (candidateNum / hosts, DC:29): a request of n candidates cut P
+                                   * ways is accepted when its last shard, n - (P-1)*floor(n/P) (it takes the remainder,
+                                   * DC:46-55), fits; with P = n_devices that holds for every
+                                   * n <= n_devices * (max_candidates - n_devices + 1) */
     int32_t workers_per_device;   /* host threads (each with its own stream) per device; 0 = default 2 */
     int32_t shard_mode;           /* ctr_shard_mode */
     int32_t min_shard_candidates; /* a request is spread over floor(n / this) GPUs, at most n_devices, at least 1
@@ -123,6 +126,36 @@ int32_t ctr_predict_async(ctr_engine* e, const int64_t* ids, const float* wts, i
 int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const float* ctx_wts, int32_t n_ctx_fields,
                                  const int64_t* cand_ids, const float* cand_wts, int64_t n_cand, float* scores_out,
                                  ctr_callback cb, void* user, ctr_ticket* ticket);
+
+/* Packed request (additive): the marshaller of sendRequest (DC:97-108) ships an int64 id and a float weight
+ * for every field slot, 12 bytes each, 468 bytes per candidate at 39 fields -- and the host link, not the GPU,
+ * bounds a request (PCIe Gen5 x16 carries ~107 M such candidates/s).  In the packed layout a per-candidate
+ * field costs a 32-bit table ROW index (the id itself for direct tables; mix64(id) & (rows-1), i.e. what the
+ * kernel would compute, for hashed ones) and a weight only if the field is flagged in weighted_mask (the
+ * others weigh 1.0, as every sparse field of the reference's own inputs does, DC:67-74):
+ * 26*4 + 13*8 = 208 bytes per candidate for the Criteo shape.  It composes with the shared context: the
+ * first n_ctx_fields are given once (original int64 ids + weights, exactly as for ctr_predict_shared_async)
+ * and cand_rows / cand_wts hold only the remaining fields: cand_rows [n_cand, F - n_ctx_fields] uint32,
+ * cand_wts [n_cand, Wk] float with Wk = number of flagged fields among the per-candidate ones, in field
+ * order (may be NULL when Wk == 0).  Scores are bit-identical to ctr_predict_async on the expanded lists.
+ * Needs a table of at most 2^32 - 1 rows.  Buffers stay owned by the caller until the ticket completes. */
+typedef struct ctr_packed_layout {
+    int32_t struct_size;      /* sizeof(ctr_packed_layout) */
+    int32_t n_ctx_fields;     /* leading fields given once per request; 0 = none */
+    uint64_t weighted_mask;   /* bit f: field f carries a per-candidate weight (bits of context fields are ignored) */
+} ctr_packed_layout;
+int32_t ctr_predict_packed_async(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ctx_ids, const float* ctx_wts,
+                                 const uint32_t* cand_rows, const float* cand_wts, int64_t n_cand, float* scores_out,
+                                 ctr_callback cb, void* user, ctr_ticket* ticket);
+
+/* The packer for callers that hold the reference's lists (ids int64 / wts float, [n_cand, F]; DC:97-108): writes
+ * the packed lists ctr_predict_packed_async takes (and the context of candidate 0 into ctx_*_out when
+ * layout->n_ctx_fields > 0).  Pure host code.  Fails with CTR_ERR_INVALID if a field the layout declares
+ * unweighted has a weight other than 1.0, or a context field differs between candidates -- the packed
+ * request would not score what the lists say.  Direct ids the table cannot hold are kept recognisable and
+ * fail the request itself, as they do in the reference layout. */
+int32_t ctr_pack_candidates(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ids, const float* wts, int64_t n_cand,
+                            uint32_t* cand_rows_out, float* cand_wts_out, int64_t* ctx_ids_out, float* ctx_wts_out);
 
 /* Blocks like CompletableFuture.join (DC:158-159).  timeout_ms < 0 waits for ever.  On
  * CTR_OK or a failure status the ticket is released; on CTR_ERR_TIMEOUT it stays valid.
@@ -186,7 +219,9 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
  * call before starting any stream capture.  All calls on a GPU share the array, which keeps the
  * previous call's contents (what has to start at zero is cleared on `stream` at the start of each
  * call): calls whose GPU work overlaps in time race -- order them on one stream or with events.
- * stream == NULL runs on the engine's stream and returns when the scores are ready. */
+ * stream == NULL runs on the engine's stream and returns when the scores are ready.  Host threads may call
+ * concurrently: the engine serialises their enqueues per GPU (and, for stream == NULL, the whole call), so
+ * two calls on one stream never interleave; calls on different caller streams still need the ordering above. */
 #define CTR_STATIC_MAX_CANDIDATES 1024
 int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, const void* d_ids, const void* d_wts,
                                 int64_t n_cand, void* d_scores, void* stream);

@@ -86,8 +86,10 @@ def proc_unit(seed: int, tag: int, idx) -> np.ndarray:
 
 
 def round_f16(x: np.ndarray) -> np.ndarray:
-    """float32 -> nearest IEEE half (ties to even, as cvt.rn.f16.f32) -> float32."""
-    return np.asarray(x, dtype=np.float32).astype(np.float16).astype(np.float32)
+    """float32 -> nearest IEEE half (ties to even) -> float32, saturating at +-65504 instead of overflowing to
+    infinity: what the kernels' cvt.rn.satfinite.f16x2.f32 does wherever an activation is stored as half."""
+    x = np.clip(np.asarray(x, dtype=np.float32), np.float32(-65504.0), np.float32(65504.0))      # NaN stays NaN
+    return x.astype(np.float16).astype(np.float32)
 
 
 # ----------------------------------------------------------------------------- spec / weights

@@ -50,7 +50,7 @@ def test_request_of_10000_sampled_against_the_oracle(full, om):
     ids, wts = om.criteo_inputs(n, seed=77, rows_per_field=ROWS_PER_FIELD)
     got = e.predict(ids, wts).copy()
     assert got.shape == (n,) and np.all(np.isfinite(got)) and got.min() >= 0 and got.max() <= 1
-    pick = np.random.default_rng(5).choice(n, 384, replace=False)
+    pick = np.random.default_rng(5).choice(n, 4094, replace=False)
     pick = np.concatenate([pick, [0, n - 1]])
     p64 = om.forward(w, ids[pick], wts[pick], "fp64")
     pemu = om.forward(w, ids[pick], wts[pick], "f16")
@@ -114,7 +114,7 @@ def test_bench_step_of_640000_device_resident(full, om):
     for r in (0, 37, 63):
         assert np.array_equal(e.predict(ids[r * n:(r + 1) * n], wts[r * n:(r + 1) * n]), allp[r * n:(r + 1) * n]), r
     # a sample across the whole step against the oracle
-    pick = np.random.default_rng(7).choice(n_req * n, 256, replace=False)
+    pick = np.random.default_rng(7).choice(n_req * n, 4096, replace=False)
     assert np.abs(allp[pick] - om.forward(w, ids[pick], wts[pick], "f16")).max() <= TOL_F16_EMU
     assert np.abs(allp[pick] - om.forward(w, ids[pick], wts[pick], "fp64")).max() <= TOL_F16
     # a second call gives the same bits (no state carried in the scratch), and so does the fixed-scratch path
@@ -125,3 +125,62 @@ def test_bench_step_of_640000_device_resident(full, om):
     e.score_device_static(d_ids.data_ptr(), d_wts.data_ptr(), 1024, d_out3.data_ptr())
     torch.cuda.synchronize()
     assert np.array_equal(d_out3.cpu().numpy(), allp[:1024])
+
+
+def test_zipf_request_against_the_oracle(full, om):
+    """SURVEY 8(d)'s "realistic" id distribution: Zipf(1.05) over each sparse field (a few hot rows, a long tail)."""
+    e, w = full
+    n = 10000
+    ids, wts = om.criteo_inputs(n, seed=81, rows_per_field=ROWS_PER_FIELD, dist="zipf")
+    got = e.predict(ids, wts).copy()
+    pick = np.random.default_rng(8).choice(n, 4096, replace=False)
+    assert np.abs(got[pick] - om.forward(w, ids[pick], wts[pick], "f16")).max() <= TOL_F16_EMU
+    assert np.abs(got[pick] - om.forward(w, ids[pick], wts[pick], "fp64")).max() <= TOL_F16
+    # the packed marshaller on the same request: same bits
+    lay = e.packed_layout(0, weighted_fields=range(13))
+    t, out = e.predict_packed_async(lay, *e.pack_candidates(lay, ids, wts))
+    assert np.array_equal(e.wait(t), got)
+
+
+def test_half_range_is_saturated_not_overflowed(full, om):
+    """A raw, un-log-scaled dense feature can push E*wt beyond 65504, the largest half.  The kernels clamp where
+    they store half (gather output, layer outputs) instead of writing +-inf, so such a candidate keeps a finite
+    score -- the one the oracle's kernel-contract mode computes with the same clamp -- and its neighbours in the
+    request are untouched."""
+    e, w = full
+    n = 512
+    ids, wts = om.criteo_inputs(n, seed=82, rows_per_field=ROWS_PER_FIELD)
+    base = e.predict(ids, wts).copy()
+    hot = wts.copy()
+    hot[5, 3] = 3.0e6                                    # |E| up to 0.25 -> |E*wt| up to 7.5e5, far beyond the half range
+    hot[77, :13] = -1.0e7
+    got = e.predict(ids, hot).copy()
+    assert np.all(np.isfinite(got)) and got.min() >= 0.0 and got.max() <= 1.0
+    keep = np.ones(n, bool)
+    keep[[5, 77]] = False
+    assert np.array_equal(got[keep], base[keep])
+    pemu = om.forward(w, ids[[5, 77]], hot[[5, 77]], "f16")
+    assert np.all(np.isfinite(pemu)) and np.abs(got[[5, 77]] - pemu).max() <= 2 * TOL_F16_EMU
+
+
+def test_config3_shape_deepfm_100k_candidates(lib_built, om, tmp_path):
+    """BASELINE config 3 on one GPU: DeepFM (624->512->512->512->1), one request of 100 000 candidates."""
+    from dtfs_b200 import binding
+    w = make_case(om.DEEPFM, hidden=(512, 512, 512), rows_per_field=1 << 20)
+    path = str(tmp_path / "deepfm.ctrw")
+    om.save_weights(w, path)
+    n = 100000
+    ids, wts = om.criteo_inputs(n, seed=83, rows_per_field=1 << 20)
+    with binding.Engine(max_candidates=n) as e:
+        e.load_weights(path)
+        got = e.predict(ids, wts).copy()
+        pick = np.random.default_rng(9).choice(n, 4096, replace=False)
+        pick[:2] = (0, n - 1)
+        assert np.abs(got[pick] - om.forward(w, ids[pick], wts[pick], "f16")).max() <= 2 * TOL_F16_EMU
+        assert np.abs(got[pick] - om.forward(w, ids[pick], wts[pick], "fp64")).max() <= TOL_F16
+        # cut 8 ways by the reference rule (what 8 GPUs would each get) and merged in order: same bits
+        merged = np.concatenate([e.predict(np.ascontiguousarray(ids[a:b]), np.ascontiguousarray(wts[a:b]))
+                                 for a, b in binding.partition_bounds(n, 8)])
+        assert np.array_equal(merged, got)
+        s, idx = e.predict_sorted(ids, wts)
+        assert np.array_equal(got[idx], s) and np.all(np.diff(s) >= 0)
