@@ -2,23 +2,42 @@
 #pragma once
 namespace {
 // ------------------------------------------------------------------ the device path for one chunk
+// Both kernels ask for the largest shared-memory carve-out: an SM configured for less by whichever kernel got
+// there first (the tower's 194 KB round up to a 196 KB carve-out, the gather's 23 KB to 32 KB) cannot take a CTA of
+// the other one until it drains, and the gather would then never run under the tower (tools/probes/
+// coresidency_probe.cu: 0 of 592 gather-sized CTAs resident beside a tower-sized one without this, all of them with it).
+template <typename Kern>
+void prefer_max_carveout(Kern k) {
+    static std::atomic<uint64_t> done{0};                     // one bit per device ordinal, per kernel instantiation
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
+    if (done.load(std::memory_order_relaxed) & (1ull << dev)) return;
+    if (cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) != cudaSuccess) (void)cudaGetLastError();
+    done.fetch_or(1ull << dev, std::memory_order_relaxed);
+}
+
+template <int TD, int IT, bool C, bool E, bool L, bool FM>
+void launch_gather_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    prefer_max_carveout(gather_pool_kernel<TD, IT, C, E, L, FM>);
+    gather_pool_kernel<TD, IT, C, E, L, FM><<<grid, kGatherThreads, smem, st>>>(gp);
+}
+
 template <int TD, int IT, bool C>
 void launch_gather_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
     switch (kind) {
-        case CTR_MODEL_LR: gather_pool_kernel<TD, IT, C, false, true, false><<<grid, kGatherThreads, smem, st>>>(gp); break;
-        case CTR_MODEL_WIDE_DEEP: gather_pool_kernel<TD, IT, C, true, true, false><<<grid, kGatherThreads, smem, st>>>(gp); break;
-        case CTR_MODEL_DEEPFM: gather_pool_kernel<TD, IT, C, true, true, true><<<grid, kGatherThreads, smem, st>>>(gp); break;
-        default: gather_pool_kernel<TD, IT, C, true, false, false><<<grid, kGatherThreads, smem, st>>>(gp); break;
+        case CTR_MODEL_LR: launch_gather_t<TD, IT, C, false, true, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_WIDE_DEEP: launch_gather_t<TD, IT, C, true, true, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_DEEPFM: launch_gather_t<TD, IT, C, true, true, true>(gp, grid, smem, st); break;
+        default: launch_gather_t<TD, IT, C, true, false, false>(gp, grid, smem, st); break;
     }
 }
 
-// Load slots per lane and candidate: fp32 rows take 4 rows per load instruction (F <= 40 -> 10 slots, else 12),
-// f16 rows 8 (F <= 40 -> 5 slots, else 6).
+// Load slots per lane and candidate: a load instruction covers 8 rows, so F <= 40 takes 5 slots and F <= 48 takes 6.
 void launch_gather(const ModelDesc& m, bool compact, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
     const bool wide = m.F > 40;
     if (m.table_dtype == CTR_TABLE_FP32) {
-        if (compact) { if (wide) launch_gather_kind<0, 12, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 10, true>(m.kind, gp, grid, smem, st); }
-        else { if (wide) launch_gather_kind<0, 12, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 10, false>(m.kind, gp, grid, smem, st); }
+        if (compact) { if (wide) launch_gather_kind<0, 6, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 5, true>(m.kind, gp, grid, smem, st); }
+        else { if (wide) launch_gather_kind<0, 6, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 5, false>(m.kind, gp, grid, smem, st); }
     } else {
         if (compact) { if (wide) launch_gather_kind<1, 6, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, 5, true>(m.kind, gp, grid, smem, st); }
         else { if (wide) launch_gather_kind<1, 6, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, 5, false>(m.kind, gp, grid, smem, st); }
@@ -29,6 +48,7 @@ void launch_gather(const ModelDesc& m, bool compact, const GatherParams& gp, int
 int32_t launch_chain(const Chain& c, const Slot& s, int n, float* d_scores, int num_sms, cudaStream_t st, long long* prof = nullptr) {
     ChainParams p = c.params;
     p.M = n;
+    p.tiles_in_flight = tiles_in_flight();
     p.prof = prof;
     if (!p.extra_out) p.scores = d_scores;
     const int tiles = (n + 2 * kBM - 1) / (2 * kBM);
@@ -74,7 +94,7 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
     const int64_t n_tiles = ((int64_t)n + kWarpTile - 1) / kWarpTile;
     static const int gather_ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : 4; }();
     const int ggrid = (int)std::max<int64_t>(1, std::min<int64_t>((n_tiles + kGatherWarps - 1) / kGatherWarps, (int64_t)dm.num_sms * gather_ctas_per_sm));
-    const size_t gsmem = (size_t)kGatherWarps * 2 * (in.ids_bytes(kWarpTile) + in.wts_bytes(kWarpTile));
+    const size_t gsmem = (size_t)kGatherWarps * gather_warp_smem(compact, m.F, in.Fk, in.Wk, in.id_bytes);
     mark(e, s, 0);
     launch_gather(m, compact, gp, ggrid, gsmem, st);
     CUDA_TRY(cudaGetLastError());

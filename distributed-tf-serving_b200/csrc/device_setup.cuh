@@ -6,6 +6,8 @@ namespace {
 template <typename Kern>
 int32_t set_smem_attr(Kern k, int bytes) {
     CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    // the whole 228 KB as shared memory, so that a gather CTA (23 KB) fits beside this kernel's 194 KB (device_path.cuh)
+    CUDA_TRY(cudaFuncSetAttribute(k, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     return CTR_OK;
 }
 
@@ -219,7 +221,7 @@ int32_t alloc_pair_scratch(ctr_engine* e, DeviceCtx& dc) {
     if (m.kind == CTR_MODEL_LR) return CTR_OK;
     CUDA_TRY(cudaSetDevice(dm.dev));
     ps.n_slices = dm.num_sms / 2;
-    const size_t rows = (size_t)ps.n_slices * 2 * 2 * kBM;            // two 256-row tiles in flight per slice
+    const size_t rows = (size_t)ps.n_slices * tiles_in_flight() * 2 * kBM;     // one or two 256-row tiles in flight per slice
     for (int l = 0; l + 1 < (int)dm.mlp.size(); ++l) ps.ld[1 + (l & 1)] = std::max(ps.ld[1 + (l & 1)], dm.mlp[l].Npad);
     if (m.kind == CTR_MODEL_DCN_V2) {
         const int xl_ld = dm.cross.empty() ? m.d_pad() : dm.cross.back().Npad;      // cross outputs may be padded past d_pad
@@ -237,8 +239,10 @@ int32_t alloc_pair_scratch(ctr_engine* e, DeviceCtx& dc) {
     // what it can for persisting lines; each stream's access window (set in init_slot_common) covers the scratch.
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, dm.dev));
-    static const bool no_persist = getenv("CTR_NO_L2_PERSIST") != nullptr;
-    if (!no_persist && prop.persistingL2CacheMaxSize > 0) {
+    // measured (profiles/r02_*): with the window on, W&D device-resident throughput FELL from 324 to 303 M candidates/s --
+    // the part of the scratch that does not fit the set-aside is treated as streaming and evicted first.  Off unless asked for.
+    static const bool persist = getenv("CTR_L2_PERSIST") != nullptr;
+    if (persist && prop.persistingL2CacheMaxSize > 0) {
         const size_t want = std::min<size_t>((size_t)prop.persistingL2CacheMaxSize, total);
         if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) != cudaSuccess) (void)cudaGetLastError();
         else dc.l2_persist_bytes = want;
@@ -304,7 +308,7 @@ int32_t build_chains(ctr_engine* e, DeviceModel& dm, Slot& s) {
             const int out = is_cross ? 3 + (l & 1) : 1 + (l & 1);
             if (s.ld[a] < L.Kpad) return fail(CTR_ERR_INVALID, "internal: activation buffer narrower than the layer's K");
             if (a == 0) rc = make_map_f16(&c.maps.a[l], s.buf[0], (uint64_t)s.x_rows, (uint64_t)L.Kpad, (uint64_t)s.ld[0], kBM);
-            else rc = make_map_tile_major(&c.maps.a[l], s.buf[a], (uint64_t)s.ld[a], (uint64_t)(2 * s.scratch_rows / kBM));   // two interleaved tiles per CTA pair
+            else rc = make_map_tile_major(&c.maps.a[l], s.buf[a], (uint64_t)s.ld[a], (uint64_t)s.scratch_tiles);
             if (rc != CTR_OK) return rc;
             if ((rc = make_map_f16(&c.maps.w[l], L.W, (uint64_t)L.Npad, (uint64_t)L.Kpad, (uint64_t)L.Kpad, c.BN / 2)) != CTR_OK) return rc;
             ChainLayer& cl = c.params.layer[l];
@@ -377,6 +381,7 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     for (int i = 1; i < 6; ++i) { s.buf[i] = ps.buf[i]; s.ld[i] = ps.ld[i]; }
     s.slice_bitmap = ps.bitmap; s.n_slices = ps.n_slices;
     s.scratch_rows = ps.n_slices * 2 * kBM;
+    s.scratch_tiles = ps.n_slices * tiles_in_flight() * 2;      // 128-row tiles in each scratch buffer
     set_scratch_window(dc, s.stream);
     return build_chains(e, dm, s);
 }

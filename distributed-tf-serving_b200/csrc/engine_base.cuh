@@ -23,6 +23,13 @@ int32_t fail(int32_t code, const std::string& msg) {
 
 inline int round_up(int x, int m) { return (x + m - 1) / m * m; }
 
+// 256-row tiles a tower CTA pair keeps in flight (tower.cuh): 2 hides the layer-boundary bubble, 1 halves the
+// activation scratch that cycles through L2.  CTR_TOWER_TILES=1|2.
+inline int tiles_in_flight() {
+    static const int v = [] { const char* c = getenv("CTR_TOWER_TILES"); return c && atoi(c) == 1 ? 1 : 2; }();
+    return v;
+}
+
 // A thread that is about to block on a condition variable first polls for this long: waking a sleeping
 // thread costs 10-20 us on each side of a request whose whole GPU time is ~60 us.  CTR_SPIN_US=0 turns
 // the polling off (hosts with fewer cores than engine threads).

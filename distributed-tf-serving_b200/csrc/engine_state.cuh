@@ -76,7 +76,8 @@ struct Slot {
     bool owns_buffers = true;  // false: the buffers are slices of the fixed scratch of ctr_score_device_static
     int64_t cap = 0;           // candidate capacity of the id/weight/score buffers
     int x_rows = 0;            // candidates per launch: rows of X / wide / extra (multiple of 256)
-    int scratch_rows = 0;      // rows of the per-pair scratch (resident CTA pairs x 256)
+    int scratch_rows = 0;      // resident CTA pairs x 256: bounds the pairs of a launch
+    int scratch_tiles = 0;     // 128-row tiles each scratch buffer holds
     int64_t* d_ids = nullptr; float* d_wts = nullptr; float* d_scores = nullptr;   // d_ids / d_wts also take the compact layouts
     float* d_wide = nullptr; float* d_extra = nullptr; int32_t* d_err = nullptr;
     __half* buf[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};

@@ -79,6 +79,7 @@ extern "C" int32_t ctr_score_device_static(ctr_engine* e, int32_t device_index, 
     Slot s;
     s.dev = dm.dev; s.stream = st; s.owns_stream = false;
     s.cap = kStaticMaxCandidates; s.x_rows = kStaticMaxCandidates; s.scratch_rows = kStaticMaxCandidates / 2;   // 2 CTA pairs x 2 tiles each
+    s.scratch_tiles = kStaticMaxCandidates / kBM;
     unsigned char* p = base;
     s.buf[0] = reinterpret_cast<__half*>(p); p += kStaticXBytes;
     s.buf[1] = reinterpret_cast<__half*>(p); p += kStaticHBytes;

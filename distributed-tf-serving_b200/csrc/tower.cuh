@@ -99,6 +99,7 @@ struct ChainParams {
     // guarantees that no other launch uses the same scratch at the same time).
     unsigned long long* slice_bitmap;
     int32_t n_slices;
+    int32_t tiles_in_flight;   // 2 (default): a pair alternates between two tiles layer by layer; 1: one tile, half the scratch
 };
 
 struct ChainMaps {
@@ -259,6 +260,7 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
     const int pair_id = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
     const int tiles_m = (p.M + 2 * kBM - 1) / (2 * kBM);            // 256-row tiles of candidates
     const int nl = p.n_layers;
+    const int tif = p.tiles_in_flight == 1 ? 1 : 2;                  // 256-row tiles a pair alternates between
 
     if (warp == 0 && lane == 0) {
         for (int l = 0; l < nl; ++l) { tma_prefetch_desc(&maps.a[l]); tma_prefetch_desc(&maps.w[l]); }
@@ -305,14 +307,14 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         {
             int s = 0; uint32_t ph = 0, ld_ph = 0;
             long long w_empty = 0, w_layer = 0;
-            for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
-                const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;             // two tiles in flight, layer by layer
+            for (int t0 = pair_id; t0 < tiles_m; t0 += tif * n_pairs) {
+                const int n_sub = (tif == 2 && t0 + n_pairs < tiles_m) ? 2 : 1;   // two tiles in flight, layer by layer
                 for (int l = 0; l < nl; ++l) {
                   for (int sub = 0; sub < n_sub; ++sub) {
                     const ChainLayer& L = p.layer[l];
                     const int t = t0 + sub * n_pairs;
                     const int a_row = t * 2 * kBM + (int)rank * kBM;          // row-major A: candidate rows
-                    const int a_tile = (slice * 2 + sub) * 2 + (int)rank;     // tile-major A: this CTA's scratch tile
+                    const int a_tile = (slice * tif + sub) * 2 + (int)rank;     // tile-major A: this CTA's scratch tile
                     const int tiles_n = (L.N + BN - 1) / BN, k_blocks = L.K / kBK;
                     for (int nt = 0; nt < tiles_n; ++nt) {
                         // the last tile of a layer may be 128 wide: each CTA then feeds the first 64 rows of its box
@@ -361,8 +363,8 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
             long long w_acc = 0, w_full = 0, t_issue = 0;
             const long long k0 = p.prof ? clock64() : 0;
             const uint64_t ns0 = p.prof ? globaltimer_ns() : 0;
-            for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
-                const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;
+            for (int t0 = pair_id; t0 < tiles_m; t0 += tif * n_pairs) {
+                const int n_sub = (tif == 2 && t0 + n_pairs < tiles_m) ? 2 : 1;
                 for (int l = 0; l < nl; ++l) {
                     const int tiles_l = (p.layer[l].N + BN - 1) / BN, k_blocks = p.layer[l].K / kBK;
                     const int tiles_n = tiles_l * n_sub;                                            // same order as the producer
@@ -419,13 +421,13 @@ tower_chain_kernel(const __grid_constant__ ChainMaps maps, const __grid_constant
         int lt = 0, dot_round = 0;
         CrossRegs x[2];
         long long w_accfull = 0, t_epi = 0;
-        for (int t0 = pair_id; t0 < tiles_m; t0 += 2 * n_pairs) {
-          const int n_sub = t0 + n_pairs < tiles_m ? 2 : 1;
+        for (int t0 = pair_id; t0 < tiles_m; t0 += tif * n_pairs) {
+          const int n_sub = (tif == 2 && t0 + n_pairs < tiles_m) ? 2 : 1;
           for (int l = 0; l < nl; ++l) {
             for (int st = 0; st < n_sub; ++st) {                                     // the two interleaved tiles of this pair
                 const int t = t0 + st * n_pairs;
                 const int grow = t * 2 * kBM + (int)rank * kBM + sub * 32 + lane;        // this thread's candidate row
-                const int stile = (slice * 2 + st) * 2 + (int)rank;                       // this CTA's 128-row scratch tile
+                const int stile = (slice * tif + st) * 2 + (int)rank;                     // this CTA's 128-row scratch tile
                 const ChainLayer& L = p.layer[l];
                 const int tiles_n = (L.N + BN - 1) / BN;
                 const bool dot_epi = L.epi == EPI_HEAD || L.epi == EPI_CROSS_DOT;

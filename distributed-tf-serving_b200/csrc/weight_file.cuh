@@ -49,7 +49,7 @@ int32_t read_weight_file(const char* path, HostWeights* hw) {
     if (m.kind < 0 || m.kind > 3) return bad("unknown model kind");
     if (m.K != kEmbDim) return bad("embedding dim must be 16");
     if (m.F < 1 || m.F > CTR_MAX_FIELDS) return bad("field count out of range (1..48)");
-    if (m.V < 1 || m.V > ((int64_t)1 << 40)) return bad("row count out of range (1 .. 2^40)");
+    if (m.V < 1 || m.V > 0xFFFFFFFEll) return bad("row count out of range (1 .. 2^32 - 2: the kernels index rows with 32 bits)");
     if (m.id_mode != CTR_ID_DIRECT && m.id_mode != CTR_ID_HASHED) return bad("unknown id mode");
     if (m.table_dtype != CTR_TABLE_FP32 && m.table_dtype != CTR_TABLE_F16) return bad("unknown table dtype");
     if (m.table_mode != 0 && m.table_mode != 1) return bad("unknown table mode (0 = raw rows in the file, 1 = procedural)");
