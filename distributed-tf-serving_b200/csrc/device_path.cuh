@@ -2,12 +2,18 @@
 #pragma once
 namespace {
 // ------------------------------------------------------------------ the device path for one chunk
-// Both kernels ask for the largest shared-memory carve-out: an SM configured for less by whichever kernel got
-// there first (the tower's 194 KB round up to a 196 KB carve-out, the gather's 23 KB to 32 KB) cannot take a CTA of
-// the other one until it drains, and the gather would then never run under the tower (tools/probes/
-// coresidency_probe.cu: 0 of 592 gather-sized CTAs resident beside a tower-sized one without this, all of them with it).
+// Shared-memory carve-out of the gather kernels.  Measured on B200 (tools/probes/coresidency_probe.cu, profiles/r02_*):
+// a gather CTA only becomes resident beside the tower's CTA when BOTH kernels prefer the largest carve-out (an SM
+// configured for the tower's 196 KB cannot take the gather's 30 KB, and the other way round, until it drains) --
+// but with the largest carve-out the gather loses its L1 (it re-reads the line of a row for the first-order weight
+// and keeps the dense fields' rows there) and runs 13 % slower (340 against 299 us per 303 104 candidates), and the
+// two kernels side by side only trade time with each other (tower 298 -> 443 us per chunk while a 175 us gather
+// hides under it).  Net: 330 M candidates/s with the driver's default carve-out against 319-325 M with co-residency,
+// so the default stays; CTR_GATHER_MAX_CARVEOUT=1 switches the co-resident configuration on.
 template <typename Kern>
 void prefer_max_carveout(Kern k) {
+    static const bool on = getenv("CTR_GATHER_MAX_CARVEOUT") != nullptr;
+    if (!on) return;
     static std::atomic<uint64_t> done{0};                     // one bit per device ordinal, per kernel instantiation
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return;
@@ -16,31 +22,67 @@ void prefer_max_carveout(Kern k) {
     done.fetch_or(1ull << dev, std::memory_order_relaxed);
 }
 
-template <int TD, int IT, bool C, bool E, bool L, bool FM>
-void launch_gather_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
-    prefer_max_carveout(gather_pool_kernel<TD, IT, C, E, L, FM>);
-    gather_pool_kernel<TD, IT, C, E, L, FM><<<grid, kGatherThreads, smem, st>>>(gp);
+// compact layouts -> warp-tile kernel
+template <int TD, int IT, bool E, bool L, bool FM>
+void launch_compact_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    if (gp.n_shards > 1) {
+        prefer_max_carveout(gather_pool_kernel<TD, IT, true, E, L, FM, true>);
+        gather_pool_kernel<TD, IT, true, E, L, FM, true><<<grid, kGatherThreads, smem, st>>>(gp);
+    } else {
+        prefer_max_carveout(gather_pool_kernel<TD, IT, true, E, L, FM, false>);
+        gather_pool_kernel<TD, IT, true, E, L, FM, false><<<grid, kGatherThreads, smem, st>>>(gp);
+    }
 }
-
-template <int TD, int IT, bool C>
-void launch_gather_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+template <int TD, int IT>
+void launch_compact_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
     switch (kind) {
-        case CTR_MODEL_LR: launch_gather_t<TD, IT, C, false, true, false>(gp, grid, smem, st); break;
-        case CTR_MODEL_WIDE_DEEP: launch_gather_t<TD, IT, C, true, true, false>(gp, grid, smem, st); break;
-        case CTR_MODEL_DEEPFM: launch_gather_t<TD, IT, C, true, true, true>(gp, grid, smem, st); break;
-        default: launch_gather_t<TD, IT, C, true, false, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_LR: launch_compact_t<TD, IT, false, true, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_WIDE_DEEP: launch_compact_t<TD, IT, true, true, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_DEEPFM: launch_compact_t<TD, IT, true, true, true>(gp, grid, smem, st); break;
+        default: launch_compact_t<TD, IT, true, false, false>(gp, grid, smem, st); break;
     }
 }
 
-// Load slots per lane and candidate: a load instruction covers 8 rows, so F <= 40 takes 5 slots and F <= 48 takes 6.
-void launch_gather(const ModelDesc& m, bool compact, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
-    const bool wide = m.F > 40;
-    if (m.table_dtype == CTR_TABLE_FP32) {
-        if (compact) { if (wide) launch_gather_kind<0, 6, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 5, true>(m.kind, gp, grid, smem, st); }
-        else { if (wide) launch_gather_kind<0, 6, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<0, 5, false>(m.kind, gp, grid, smem, st); }
+// reference layout -> block-tile kernel
+template <int TD, bool H, bool E, bool L, bool FM>
+void launch_tile_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    if (gp.n_shards > 1) {
+        prefer_max_carveout(gather_tile_kernel<TD, H, E, L, FM, true>);
+        gather_tile_kernel<TD, H, E, L, FM, true><<<grid, kTileThreads, smem, st>>>(gp);
     } else {
-        if (compact) { if (wide) launch_gather_kind<1, 6, true>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, 5, true>(m.kind, gp, grid, smem, st); }
-        else { if (wide) launch_gather_kind<1, 6, false>(m.kind, gp, grid, smem, st); else launch_gather_kind<1, 5, false>(m.kind, gp, grid, smem, st); }
+        prefer_max_carveout(gather_tile_kernel<TD, H, E, L, FM, false>);
+        gather_tile_kernel<TD, H, E, L, FM, false><<<grid, kTileThreads, smem, st>>>(gp);
+    }
+}
+template <int TD, bool H>
+void launch_tile_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
+    switch (kind) {
+        case CTR_MODEL_LR: launch_tile_t<TD, H, false, true, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_WIDE_DEEP: launch_tile_t<TD, H, true, true, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_DEEPFM: launch_tile_t<TD, H, true, true, true>(gp, grid, smem, st); break;
+        default: launch_tile_t<TD, H, true, false, false>(gp, grid, smem, st); break;
+    }
+}
+
+// The gather of n candidates on `st`.  Reference layout: block-tile kernel (32-candidate tiles).  Compact layouts:
+// warp-tile kernel (a load instruction covers 8 rows, so F <= 40 takes 5 slots per lane and F <= 48 takes 6).
+void launch_gather(const ModelDesc& m, bool compact, const GatherParams& gp, int n, int num_sms, cudaStream_t st) {
+    static const int ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : 4; }();
+    const bool f32 = m.table_dtype == CTR_TABLE_FP32;
+    if (compact) {
+        const int64_t n_tiles = ((int64_t)n + kWarpTile - 1) / kWarpTile;
+        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n_tiles + kGatherWarps - 1) / kGatherWarps, (int64_t)num_sms * ctas_per_sm));
+        const size_t smem = (size_t)kGatherWarps * gather_warp_smem(true, m.F, gp.Fk, gp.Wk, gp.id_bytes);
+        const bool wide = m.F > 40;
+        if (f32) { if (wide) launch_compact_kind<0, 6>(m.kind, gp, grid, smem, st); else launch_compact_kind<0, 5>(m.kind, gp, grid, smem, st); }
+        else { if (wide) launch_compact_kind<1, 6>(m.kind, gp, grid, smem, st); else launch_compact_kind<1, 5>(m.kind, gp, grid, smem, st); }
+    } else {
+        const int n_tiles = (n + kGatherTile - 1) / kGatherTile;
+        const int grid = std::max(1, std::min(n_tiles, num_sms * ctas_per_sm));
+        const size_t smem = (size_t)2 * kGatherTile * m.F * 12;
+        const bool hashed = gp.hashed != 0;
+        if (f32) { if (hashed) launch_tile_kind<0, true>(m.kind, gp, grid, smem, st); else launch_tile_kind<0, false>(m.kind, gp, grid, smem, st); }
+        else { if (hashed) launch_tile_kind<1, true>(m.kind, gp, grid, smem, st); else launch_tile_kind<1, false>(m.kind, gp, grid, smem, st); }
     }
 }
 
@@ -91,12 +133,8 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
     for (int g = 0; g < CTR_MAX_DEVICES; ++g) gp.shard_base[g] = e->shard_base[g];
     if (m.kind == CTR_MODEL_LR) { gp.scores = d_scores; }
     else { gp.X = s.buf[0]; gp.ldx = s.ld[0]; gp.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide; }
-    const int64_t n_tiles = ((int64_t)n + kWarpTile - 1) / kWarpTile;
-    static const int gather_ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : 4; }();
-    const int ggrid = (int)std::max<int64_t>(1, std::min<int64_t>((n_tiles + kGatherWarps - 1) / kGatherWarps, (int64_t)dm.num_sms * gather_ctas_per_sm));
-    const size_t gsmem = (size_t)kGatherWarps * gather_warp_smem(compact, m.F, in.Fk, in.Wk, in.id_bytes);
     mark(e, s, 0);
-    launch_gather(m, compact, gp, ggrid, gsmem, st);
+    launch_gather(m, compact, gp, n, dm.num_sms, st);
     CUDA_TRY(cudaGetLastError());
     e->launches.fetch_add(1, std::memory_order_relaxed);
     int li = 0;

@@ -32,7 +32,7 @@
 // (already hashed by the host packer), and weights only for the fields flagged in weighted_mask (the
 // others are 1.0) -- what ctr_predict_shared_async / ctr_predict_packed_async ship over the host link.
 //
-// Footprint: 192 threads x 80 registers and ~23 KB of shared memory per CTA, so that one CTA fits on an SM
+// Footprint: 256 threads x 64 registers and ~30 KB of shared memory per CTA, so that one CTA fits on an SM
 // NEXT TO the resident tower CTA (tower.cuh) and a chunk's gather runs under the previous chunk's tower.
 //
 // Roofline: HBM.  Algorithmic bytes per candidate (F=39: 13 dense + 26 sparse, fp32 table):
@@ -43,7 +43,7 @@
 namespace ctr {
 
 constexpr int kWarpTile = 4;           // candidates per warp tile
-constexpr int kGatherThreads = 192;    // 6 independent warps x 80 registers: 15 K registers, what the tower leaves free on its SM
+constexpr int kGatherThreads = 256;    // 8 independent warps x 64 registers: the 16 K registers the tower leaves free on its SM
 constexpr int kGatherWarps = kGatherThreads / 32;
 
 struct GatherParams {
@@ -76,50 +76,244 @@ struct GatherParams {
 template <int kTableDtype>
 struct RowLayout;
 template <>
-struct RowLayout<0> { static constexpr int shift = 7; static constexpr int w1_off = 64; static constexpr int lane_bytes = 32; };
+struct RowLayout<0> { static constexpr int shift = 7; static constexpr int w1_off = 64; };
 template <>
-struct RowLayout<1> { static constexpr int shift = 6; static constexpr int w1_off = 32; static constexpr int lane_bytes = 16; };
+struct RowLayout<1> { static constexpr int shift = 6; static constexpr int w1_off = 32; };
 
-constexpr int kLanesPerRow = 4;                    // lane q of a group: 0, 1 = embedding halves, 2 = first-order weight, 3 idle
+// ------------------------------------------------------------------ reference layout: the block-tile kernel
+// ids int64 [n, F] / wts float [n, F] exactly as sendRequest ships them (DC:97-108).  A CTA stages the lists of a
+// 32-candidate tile with two bulk copies (double buffered), a warp takes a candidate: 8 lane groups x 4 lanes, lane
+// q of a group loads embedding values 4q .. 4q+3 of the group's row (128-bit) and lane 0 the first-order weight;
+// all rounds' loads are issued before any is used.  Same lanes, same order of operations, same shuffle tree as the
+// warp-tile kernel below (which serves the compact layouts): the two give bit-identical results.
+constexpr int kGatherTile = 32;        // candidates per staged tile
+constexpr int kTileThreads = 256;      // 8 warps -> 4 candidates per warp per tile
+constexpr int kGatherRounds = 6;       // 8 fields per round -> F <= 48
+
+__device__ __forceinline__ float4 ldg_nc_f4(const void* p) {
+    float4 v;
+    asm volatile("ld.global.nc.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint2 ldg_nc_u2(const void* p) {
+    uint2 v;
+    asm volatile("ld.global.nc.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ldg_nc_f1(const void* p) {
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
+template <int kTableDtype, bool kHashed, bool kEmb, bool kLin, bool kFM, bool kSharded>
+__global__ void __launch_bounds__(kTileThreads, 4)
+gather_tile_kernel(const __grid_constant__ GatherParams p) {
+    extern __shared__ __align__(128) uint8_t gsm[];
+    const int F = p.F;
+    const int64_t* const gids = static_cast<const int64_t*>(p.ids);
+    const uint32_t ids_bytes = kGatherTile * F * 8, wts_bytes = kGatherTile * F * 4;
+    // [ids buf0 | ids buf1 | wts buf0 | wts buf1]; pointer arithmetic (not arrays) keeps this out of local memory
+    auto ids_buf = [&](int buf) { return reinterpret_cast<int64_t*>(gsm + buf * ids_bytes); };
+    auto wts_buf = [&](int buf) { return reinterpret_cast<float*>(gsm + 2 * ids_bytes + buf * wts_bytes); };
+    __shared__ __align__(8) uint64_t full_bar[2];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, q = lane & 3;
+    const int64_t n_tiles = (p.n + kGatherTile - 1) / kGatherTile;
+
+    if (tid == 0) {
+        mbar_init(&full_bar[0], 1);
+        mbar_init(&full_bar[1], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    // Stage the id / weight lists of one tile.  Full, aligned tiles: one elected thread
+    // issues two bulk copies that complete on full_bar[buf].  The ragged last tile (or
+    // unaligned caller pointers) falls back to ordinary loads by the whole CTA.
+    auto tile_is_bulk = [&](int64_t tile) { return p.bulk_ok && (tile + 1) * kGatherTile <= p.n; };
+    auto stage = [&](int64_t tile, int buf) {
+        const int64_t c0 = tile * kGatherTile;
+        if (tile_is_bulk(tile)) {
+            if (tid == 0) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                mbar_expect_tx(&full_bar[buf], ids_bytes + wts_bytes);
+                bulk_g2s(ids_buf(buf), gids + c0 * F, ids_bytes, &full_bar[buf]);
+                bulk_g2s(wts_buf(buf), p.wts + c0 * F, wts_bytes, &full_bar[buf]);
+            }
+        } else {
+            const int64_t cnt = min((int64_t)kGatherTile, p.n - c0) * F;
+            int64_t* di = ids_buf(buf);
+            float* dw = wts_buf(buf);
+            for (int64_t i = tid; i < cnt; i += kTileThreads) {
+                di[i] = gids[c0 * F + i];
+                dw[i] = p.wts[c0 * F + i];
+            }
+        }
+    };
+
+    uint32_t phase_bits = 0;                               // bit b = parity to wait for on full_bar[b]
+    int64_t tile = blockIdx.x;
+    if (tile < n_tiles) stage(tile, 0);
+    __syncthreads();
+
+    for (int it = 0; tile < n_tiles; tile += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const int64_t next = tile + gridDim.x;
+        if (next < n_tiles) stage(next, buf ^ 1);          // buf^1 was released by the barrier below
+        if (tile_is_bulk(tile)) {
+            mbar_wait(&full_bar[buf], (phase_bits >> buf) & 1u);
+            phase_bits ^= 1u << buf;
+        }
+        const int64_t c0 = tile * kGatherTile;
+        const int n_here = (int)min((int64_t)kGatherTile, p.n - c0);
+
+        for (int c = warp; c < n_here; c += kTileThreads / 32) {
+            const int64_t b = c0 + c;
+            const int64_t* sid = ids_buf(buf) + c * F;
+            const float* swt = wts_buf(buf) + c * F;
+
+            float4 ev[kGatherRounds];
+            float wv[kGatherRounds], w1v[kGatherRounds];
+#pragma unroll
+            for (int r = 0; r < kGatherRounds; ++r) {
+                ev[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+                wv[r] = 0.f;
+                w1v[r] = 0.f;
+                const int f = r * 8 + g;
+                if (r * 8 < F && f < F) {
+                    const int64_t id = sid[f];
+                    wv[r] = swt[f];
+                    uint64_t row;
+                    if (kHashed) {
+                        row = mix64((uint64_t)id) & (p.num_rows - 1);
+                    } else {
+                        row = (uint64_t)id;
+                        if (row >= p.num_rows) { row = 0; wv[r] = 0.f; *p.error_flag = 1; }
+                    }
+                    const uint8_t* base = p.table;
+                    if (kSharded) {
+                        const uint32_t owner = (uint32_t)(row % (uint32_t)p.n_shards);
+                        row = row / (uint32_t)p.n_shards;
+                        base = p.shard_base[owner];
+                    }
+                    const uint8_t* rp = base + (row << RowLayout<kTableDtype>::shift);
+                    if (kEmb || kFM) {
+                        if (kTableDtype == 0) {
+                            ev[r] = ldg_nc_f4(rp + q * 16);
+                        } else {
+                            const uint2 h = ldg_nc_u2(rp + q * 8);
+                            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&h.x));
+                            const float2 c2 = __half22float2(*reinterpret_cast<const __half2*>(&h.y));
+                            ev[r] = make_float4(a.x, a.y, c2.x, c2.y);
+                        }
+                    }
+                    if (kLin && q == 0) w1v[r] = ldg_nc_f1(rp + RowLayout<kTableDtype>::w1_off);
+                }
+            }
+
+            float lin = 0.f, s2 = 0.f;
+            float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int r = 0; r < kGatherRounds; ++r) {
+                const int f = r * 8 + g;
+                if (r * 8 < F) {
+                    const float wt = wv[r];
+                    const float4 x = make_float4(ev[r].x * wt, ev[r].y * wt, ev[r].z * wt, ev[r].w * wt);
+                    if (kLin) lin = fmaf(w1v[r], wt, lin);
+                    if (kFM) {
+                        s1.x += x.x; s1.y += x.y; s1.z += x.z; s1.w += x.w;
+                        s2 = fmaf(x.x, x.x, s2); s2 = fmaf(x.y, x.y, s2); s2 = fmaf(x.z, x.z, s2); s2 = fmaf(x.w, x.w, s2);
+                    }
+                    if (kEmb && f < F) {
+                        uint2 o;                                 // saturating: beyond the half range -> +-65504, never inf
+                        o.x = pack_half2_sat(x.x, x.y);
+                        o.y = pack_half2_sat(x.z, x.w);
+                        *reinterpret_cast<uint2*>(p.X + b * p.ldx + f * kEmbDim + q * 4) = o;
+                    }
+                }
+            }
+
+            if (kLin || kFM) {
+                float acc = lin;                              // only q==0 lanes hold first-order terms
+                if (kFM) {
+                    // field sums per embedding coordinate: reduce over the 8 lane groups
+#pragma unroll
+                    for (int off = 4; off <= 16; off <<= 1) {
+                        s1.x += __shfl_xor_sync(0xffffffffu, s1.x, off);
+                        s1.y += __shfl_xor_sync(0xffffffffu, s1.y, off);
+                        s1.z += __shfl_xor_sync(0xffffffffu, s1.z, off);
+                        s1.w += __shfl_xor_sync(0xffffffffu, s1.w, off);
+                    }
+                    const float sq = s1.x * s1.x + s1.y * s1.y + s1.z * s1.z + s1.w * s1.w;
+                    acc += (g == 0 ? 0.5f * sq : 0.f) - 0.5f * s2;
+                }
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+                if (lane == 0) {
+                    const float z = acc + p.b0;
+                    if (p.wide) p.wide[b] = z;
+                    if (p.scores) p.scores[b] = sigmoidf_fast(z);
+                }
+            }
+        }
+        __syncthreads();   // every warp is done with buf before it is staged again
+    }
+}
+
+
+// ------------------------------------------------------------------ compact layouts: the warp-tile kernel
+constexpr int kLanesPerRow = 4;
 constexpr int kRowsPerLoad = 32 / kLanesPerRow;    // 8 rows per load instruction
 
-// One lane's piece of a packed row.  fp32 rows: 32 bytes (one 256-bit load, SASS LDG.E.256) -- lanes 0-2 of a group
-// cover [e0..e7 | e8..e15 | w1, pad]; f16 rows: 16 bytes -- [e0..e7 | e8..e15 | w1, pad].  The load is predicated
-// (no branch: a lane that does not load keeps what it has) and does not allocate in L1: a row is used once.
+// One lane's piece of a packed row.  Loads are predicated (no branch: a lane that does not load keeps what it has)
+// and do not allocate in L1: a row is used once.
+//   fp32 rows: lane q of a group takes embedding values 4q .. 4q+3 (one 128-bit load; the four lanes cover the 64
+//              bytes of the embedding) and lane 0 also takes the first-order weight (one 32-bit load): 5 registers a
+//              slot, so that a window of 40 rows per warp fits the 64 registers that let 32 warps live on an SM.
+//              (A variant with one 256-bit load per lane -- row and weight in one instruction -- needed 8 registers
+//              a slot, ran at 24 warps per SM and was slower: the kernel lives on rows in flight.)
+//   f16 rows:  the same mapping with 64-bit loads (4 halfs per lane).
 template <int kTableDtype>
 struct RowPiece;
 template <>
 struct RowPiece<0> {
-    uint32_t r[8];
-    __device__ __forceinline__ void zero() {
-#pragma unroll
-        for (int k = 0; k < 8; ++k) r[k] = 0u;
-    }
-    __device__ __forceinline__ void load(const void* p, bool on) {
-        asm volatile("{\n\t.reg .pred P;\n\tsetp.ne.u32 P, %9, 0;\n\t"
-                     "@P ld.global.nc.L1::no_allocate.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n\t}"
-                     : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]) : "l"(p), "r"((uint32_t)on));
+    static constexpr int nv = 4;                   // embedding values per embedding lane
+    static constexpr int emb_lanes = 4;
+    static constexpr int w1_lane = 0;
+    uint32_t r[4];
+    uint32_t w;
+    __device__ __forceinline__ void zero() { r[0] = r[1] = r[2] = r[3] = 0u; w = 0u; }
+    __device__ __forceinline__ void load(const uint8_t* row, int q, bool emb_on, bool w1_on) {
+        asm volatile("{\n\t.reg .pred P, Q;\n\tsetp.ne.u32 P, %7, 0;\n\tsetp.ne.u32 Q, %8, 0;\n\t"
+                     "@P ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%5];\n\t"
+                     "@Q ld.global.nc.u32 %4, [%6];\n\t}"
+                     : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(w)
+                     : "l"(row + q * 16), "l"(row + 64), "r"((uint32_t)emb_on), "r"((uint32_t)w1_on));
     }
     __device__ __forceinline__ float val(int k) const { return __uint_as_float(r[k]); }
-    __device__ __forceinline__ float w1() const { return __uint_as_float(r[0]); }
+    __device__ __forceinline__ float w1() const { return __uint_as_float(w); }
 };
 template <>
 struct RowPiece<1> {
-    uint32_t r[4];
-    __device__ __forceinline__ void zero() {
-#pragma unroll
-        for (int k = 0; k < 4; ++k) r[k] = 0u;
-    }
-    __device__ __forceinline__ void load(const void* p, bool on) {
-        asm volatile("{\n\t.reg .pred P;\n\tsetp.ne.u32 P, %5, 0;\n\t"
-                     "@P ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];\n\t}"
-                     : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]) : "l"(p), "r"((uint32_t)on));
+    static constexpr int nv = 4;
+    static constexpr int emb_lanes = 4;
+    static constexpr int w1_lane = 0;
+    uint32_t r[2];
+    uint32_t w;
+    __device__ __forceinline__ void zero() { r[0] = r[1] = 0u; w = 0u; }
+    __device__ __forceinline__ void load(const uint8_t* row, int q, bool emb_on, bool w1_on) {
+        asm volatile("{\n\t.reg .pred P, Q;\n\tsetp.ne.u32 P, %5, 0;\n\tsetp.ne.u32 Q, %6, 0;\n\t"
+                     "@P ld.global.nc.v2.u32 {%0,%1}, [%3];\n\t"
+                     "@Q ld.global.nc.u32 %2, [%4];\n\t}"
+                     : "+r"(r[0]), "+r"(r[1]), "+r"(w) : "l"(row + q * 8), "l"(row + 32), "r"((uint32_t)emb_on), "r"((uint32_t)w1_on));
     }
     __device__ __forceinline__ float val(int k) const {
         const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&r[k >> 1]));
         return (k & 1) ? a.y : a.x;
     }
-    __device__ __forceinline__ float w1() const { return __uint_as_float(r[0]); }
+    __device__ __forceinline__ float w1() const { return __uint_as_float(w); }
 };
 
 // Shared memory of one warp (bytes): the raw id / weight lists as they arrive, and the expanded {row, weight} entries.
@@ -132,8 +326,8 @@ __host__ __device__ inline uint32_t gather_warp_smem(bool compact, int F, int Fk
 
 // kTableDtype: 0 fp32 rows, 1 f16 rows.  kIters: load slots per lane and candidate (kIters * 8 >= F).
 // kCompact: compact input (shared context / uint32 rows / sparse weights).  kEmb: write X.  kLin: first-order
-// sum.  kFM: DeepFM second-order term.
-template <int kTableDtype, int kIters, bool kCompact, bool kEmb, bool kLin, bool kFM>
+// sum.  kFM: DeepFM second-order term.  kSharded: rows striped over the devices (row mod n_shards), read through peer pointers.
+template <int kTableDtype, int kIters, bool kCompact, bool kEmb, bool kLin, bool kFM, bool kSharded>
 __global__ void __launch_bounds__(kGatherThreads, 4)
 gather_pool_kernel(const __grid_constant__ GatherParams p) {
     using RL = RowLayout<kTableDtype>;
@@ -222,19 +416,22 @@ gather_pool_kernel(const __grid_constant__ GatherParams p) {
     };
 
     // ---- gather phase: straight-line code, no branch inside a candidate.
+    constexpr int NV = Piece::nv;
     Piece ev[kIters];                                          // the rolling window: slot j = row of field j*8 + g
-    const bool emb_lane = q < 2, w1_lane = q == 2;
-    const bool load_lane = (emb_lane && (kEmb || kFM)) || (w1_lane && kLin);
-    const uint32_t lane_off = (uint32_t)q * RL::lane_bytes;
+    const bool emb_lane = q < Piece::emb_lanes, w1_lane = q == Piece::w1_lane;
+    const bool emb_on = emb_lane && (kEmb || kFM), w1_on = w1_lane && kLin;
     uint32_t slot_mask = 0;                                    // bit j: field j*8 + g exists
 #pragma unroll
     for (int j = 0; j < kIters; ++j) slot_mask |= (j * kRowsPerLoad + g < F ? 1u : 0u) << j;
 #pragma unroll
     for (int j = 0; j < kIters; ++j) ev[j].zero();             // lanes / slots that never load keep zeros for good
 
-    // the entries {row, weight} of the candidate at shared address e0, one per slot of this lane; a slot that does
-    // not exist for this lane reads as {0, 0.0f}.  All slots are fetched together: one shared-memory latency per
-    // candidate, not one in front of every load
+    // the entries {row, weight} of the candidate whose entry of field g is at shared address e0, one per slot of this
+    // lane ({0, 0.0f} for a slot the lane does not have).  Fetched together in front of the candidate's loads: inside
+    // the consume / issue sequence below the only long-latency instructions left are the row loads themselves, so
+    // that each slot's loads can have a scoreboard of their own (tools/sass_scoreboards.py: with the shared-memory
+    // reads and the shard arithmetic in between, ptxas put every row load on ONE scoreboard, and waiting for the
+    // oldest load then also waited for the newest -- one full DRAM latency per slot)
     auto lds_entries = [&](uint32_t e0, uint2 (&ent)[kIters]) {
 #pragma unroll
         for (int j = 0; j < kIters; ++j) {
@@ -243,43 +440,47 @@ gather_pool_kernel(const __grid_constant__ GatherParams p) {
                          : "+r"(ent[j].x), "+r"(ent[j].y) : "r"(e0 + j * (kRowsPerLoad * 8)), "r"((slot_mask >> j) & 1u));
         }
     };
-    // issue the load of slot j: table row `row`
+    // issue the loads of slot j: table row `row`
     auto issue = [&](int j, uint32_t row) {
+        const bool on = (slot_mask >> j) & 1u;
         const uint8_t* base = p.table;
-        if (p.n_shards > 1) {
+        if (kSharded) {
             base = p.shard_base[row % (uint32_t)p.n_shards];
             row = row / (uint32_t)p.n_shards;
         }
-        ev[j].load(base + (((uint64_t)row << RL::shift) | lane_off), load_lane && ((slot_mask >> j) & 1u));
+        ev[j].load(base + ((uint64_t)row << RL::shift), q, emb_on && on, w1_on && on);
     };
 
     // per-candidate accumulators (of the candidate being consumed)
-    float lin, s2, s1[8];
+    float lin, s2, s1[NV];
     auto reset_acc = [&]() {
         lin = 0.f; s2 = 0.f;
 #pragma unroll
-        for (int k = 0; k < 8; ++k) s1[k] = 0.f;
+        for (int k = 0; k < NV; ++k) s1[k] = 0.f;
     };
     // consume slot j (weight wt; 0 for a slot this lane does not have) of the candidate whose X piece starts at xrow
     auto consume = [&](int j, float wt, __half* xrow) {
         if (kEmb || kFM) {
-            float x[8];
+            float x[NV];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) x[k] = ev[j].val(k) * wt;      // every lane: the idle lanes' products go nowhere
+            for (int k = 0; k < NV; ++k) x[k] = ev[j].val(k) * wt;     // every lane: the idle lanes' products go nowhere
             if (kFM) {
-                if (emb_lane) {                                        // (the w1 lane holds pad bytes, not embedding values)
+                if (emb_lane) {                                        // (in f16 rows the w1 lane holds pad bytes, not values)
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) { s1[k] += x[k]; s2 = fmaf(x[k], x[k], s2); }
+                    for (int k = 0; k < NV; ++k) { s1[k] += x[k]; s2 = fmaf(x[k], x[k], s2); }
                 }
             }
             if (kEmb) {
-                uint4 o;
-                o.x = pack_half2_sat(x[0], x[1]); o.y = pack_half2_sat(x[2], x[3]);
-                o.z = pack_half2_sat(x[4], x[5]); o.w = pack_half2_sat(x[6], x[7]);
-                if (emb_lane && ((slot_mask >> j) & 1u)) *reinterpret_cast<uint4*>(xrow + j * (kRowsPerLoad * kEmbDim)) = o;
+                uint32_t o[NV / 2];
+#pragma unroll
+                for (int k = 0; k < NV / 2; ++k) o[k] = pack_half2_sat(x[2 * k], x[2 * k + 1]);
+                if (emb_lane && ((slot_mask >> j) & 1u)) {
+                    __half* dst = xrow + j * (kRowsPerLoad * kEmbDim);
+                    *reinterpret_cast<uint2*>(dst) = make_uint2(o[0], o[1]);
+                }
             }
         }
-        if (kLin) lin = fmaf(ev[j].w1(), w1_lane ? wt : 0.f, lin);     // embedding lanes: a finite value times zero
+        if (kLin) lin = fmaf(ev[j].w1(), w1_lane ? wt : 0.f, lin);     // other lanes: a finite value (or zero) times zero
     };
     // after the last slot of a candidate: pool over the warp and write lin (+FM) / the LR score
     auto finish = [&](int b) {
@@ -290,17 +491,15 @@ gather_pool_kernel(const __grid_constant__ GatherParams p) {
 #pragma unroll
                 for (int off = kLanesPerRow; off <= 16; off <<= 1) {
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], off);
+                    for (int k = 0; k < NV; ++k) s1[k] += __shfl_xor_sync(0xffffffffu, s1[k], off);
                 }
-                float sq = 0.f;
-#pragma unroll
-                for (int k = 0; k < 8; ++k) sq = fmaf(s1[k], s1[k], sq);
+                const float sq = s1[0] * s1[0] + s1[1] * s1[1] + s1[2] * s1[2] + s1[3] * s1[3];     // as the tile kernel writes it
                 acc += (g == 0 && emb_lane ? 0.5f * sq : 0.f) - 0.5f * s2;
             }
-            // first-order terms live in the q == 2 lanes only: without FM three steps over the lane groups are enough
+            // first-order terms live in one lane of every group: without FM three steps over the lane groups are enough
 #pragma unroll
             for (int off = 16; off >= (kFM ? 1 : kLanesPerRow); off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
-            if (lane == (kFM ? 0 : 2)) {
+            if (lane == (kFM ? 0 : Piece::w1_lane)) {
                 const float z = acc + p.b0;
                 if (p.wide) p.wide[b] = z;
                 if (p.scores) p.scores[b] = sigmoidf_fast(z);
@@ -335,7 +534,7 @@ gather_pool_kernel(const __grid_constant__ GatherParams p) {
     int prev_b = 0;                                        // its index in this launch
 #pragma unroll
     for (int j = 0; j < kIters; ++j) prev_wt[j] = 0.f;
-    const int xlane = g * kEmbDim + q * 8;                 // this lane's 8 halfs of field g within a row of X
+    const int xlane = g * kEmbDim + q * NV;                // this lane's halfs of field g within a row of X
     for (int it = 0; tile < n_tiles; tile += tile_stride, ++it) {
         const int bsel = it & 1;
         const int c0 = tile * kWarpTile;
