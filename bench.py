@@ -24,6 +24,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
+import subprocess
 import sys
 import tempfile
 import threading
@@ -66,6 +67,32 @@ def model_flop_per_candidate(model: str) -> int:
     return fl + 2 * (m["hidden"][-1] + (d if m["kind"] == 3 else 0))
 
 
+def tower_name(model: str) -> str:
+    m = MODELS[model]
+    return "624->" + "->".join(map(str, m["hidden"])) + "->1" + (" + %d cross layers 624x624" % m["n_cross"] if m["n_cross"] else "")
+
+
+def num_table_rows(rows_per_field: int, hashed: bool) -> int:
+    n = N_DENSE + 1 + N_SPARSE * rows_per_field
+    return 1 << int(np.ceil(np.log2(n))) if hashed else n
+
+
+WORKLOAD = "wide_deep criteo 13 dense + 26 sparse dim16, 10k-candidate requests (BASELINE config 2)"
+
+
+def workload_config(args, world: int) -> dict:
+    """The `config` block: identical keys and values in both arms (ours / --impl reference)."""
+    rows = num_table_rows(args.rows_per_field, args.hashed)
+    row_bytes = 64 if args.table_dtype == "f16" else 128
+    C, R = args.candidates, args.requests_per_step
+    return {"workload": WORKLOAD, "model": args.model, "tower": tower_name(args.model),
+            "id_mode": "hashed" if args.hashed else "direct", "candidates_per_request": C, "requests_per_step": R,
+            "candidates_per_step_per_gpu": C * R, "table_rows": int(rows), "table_dtype": args.table_dtype,
+            "table_bytes_per_gpu": int(rows * row_bytes), "id_distribution": "uniform",
+            "l2": "inputs larger than L2 (%.0f MB ids+weights per step; %.1f GB table, random rows)" % (C * R * F * 12 / 1e6, rows * row_bytes / 1e9),
+            "parallelism": "candidate-sharded x%d, tables replicated, no collective" % world}
+
+
 def write_model(path: str, rows_per_field: int, seed: int = 1234, model: str = "wide_deep", table_dtype: int = 0, hashed: bool = False):
     """Random-init model of the named architecture; procedural table (no multi-GB file)."""
     from dtfs_b200 import weights as W
@@ -80,9 +107,7 @@ def write_model(path: str, rows_per_field: int, seed: int = 1234, model: str = "
     cross = [(rng.uniform(-0.03, 0.03, (d, d)).astype(np.float32), rng.uniform(-0.05, 0.05, d).astype(np.float32))
              for _ in range(m["n_cross"])]
     w_out = rng.uniform(-1, 1, m["hidden"][-1] + (d if m["kind"] == 3 else 0)).astype(np.float32)
-    num_rows = N_DENSE + 1 + N_SPARSE * rows_per_field
-    if hashed:
-        num_rows = 1 << int(np.ceil(np.log2(num_rows)))
+    num_rows = num_table_rows(rows_per_field, hashed)
     W.write_weight_file(path, model_kind=m["kind"], num_fields=F, num_rows=num_rows, b0=0.01, table_dtype=table_dtype,
                         id_mode=W.ID_HASHED if hashed else W.ID_DIRECT, seed=seed, scale_e=0.25, scale_w1=0.5,
                         mlp=mlp, cross=cross, w_out=w_out, b_out=-0.02)
@@ -140,22 +165,46 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.samples)}
 
 
-def cpu_restatement(weight_path: str, rows_per_field: int, n_cand: int, n_requests: int, warmup: int):
-    """The oracle's CPU port of one reference request (the only place bench.py executes oracle/)."""
-    import psutil
-    from oracle import cpu_baseline as cb, model as om
-    w = om.load_weights(weight_path)
-    need = w.spec.num_rows * 68
-    cap = None
-    if psutil.virtual_memory().available < need * 1.5 + (8 << 30):
-        cap = N_DENSE + 1 + N_SPARSE * (1 << 18)
-    client = cb.CpuClient(w, n_shards=2, with_wire=True, table_rows_cap=cap)
-    ids, wts = om.criteo_inputs(n_cand, seed=4321, rows_per_field=rows_per_field)
-    sec = cb.time_requests(client, ids, wts, n_requests, warmup)
-    note = client.server.table_note
-    cores = client.cores
-    client.close()
-    return sec, cores, note
+def cpu_baseline_subprocess(args):
+    """The CPU baseline of the repo arm = the reference arm on a bounded sample, in its own process (so that this
+    process never loads anything under oracle/)."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--steps", "12", "--warmup", "1",
+           "--ref-requests-per-step", "20", "--candidates", str(args.candidates), "--rows-per-field", str(args.rows_per_field),
+           "--requests-per-step", str(args.requests_per_step)]
+    env = dict(os.environ)
+    for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "OMP_NUM_THREADS"):
+        env.pop(k, None)
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=900, env=env)
+        for ln in reversed(out.stdout.splitlines()):
+            if ln.startswith("{"):
+                return json.loads(ln)["cpu_baseline"]
+        return {"value": None, "unit": "candidates/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: " + out.stderr[-300:]}
+    except Exception as ex:  # noqa: BLE001
+        return {"value": None, "unit": "candidates/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (ex,)}
+
+
+def closed_loop_latency(wpath: str, args, workers: int):
+    """p50 / p99 of a 10 000-candidate request under the reference's load shape (DCNClient.java:30-31, :213-224):
+    6 closed-loop client threads, 10 000 timed requests after 1 000 warm-up, C++ over the C ABI."""
+    from dtfs_b200 import build
+    exe = build.build_stream_sweep()
+    C = args.candidates
+    cmd = [exe, "--weights", wpath, "--lib", build.LIB, "--threads", "6", "--requests", str(args.closed_loop_requests), "--warmup", "1000",
+           "--min", str(C), "--max", str(C), "--rows-per-field", str(args.rows_per_field), "--workers", str(workers)]
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        for ln in out.stdout.splitlines():
+            cells = [c.strip() for c in ln.strip().strip("|").split("|")]
+            if len(cells) >= 9 and cells[0] == str(C):
+                return {"p50_ms": float(cells[1]), "p99_ms": float(cells[2]), "requests_per_s": float(cells[3]), "clients": 6,
+                        "timed_requests": args.closed_loop_requests, "warmup_requests": 1000,
+                        "open_loop_70pct": {"requests_per_s": float(cells[6]), "p50_ms": float(cells[7]), "p99_ms": float(cells[8])},
+                        "what": "%d-candidate requests, 6 closed-loop client threads (DCNClient.java:213-224), ctr_predict_async + ctr_wait from pinned "
+                                "buffers; open loop: Poisson arrivals at 70%% of the closed-loop rate, latency from the scheduled arrival" % C}
+        return {"error": (out.stderr or out.stdout)[-300:]}
+    except Exception as ex:  # noqa: BLE001
+        return {"error": repr(ex)}
 
 
 def run_reference(args, rank, world):
@@ -168,7 +217,8 @@ def run_reference(args, rank, world):
     path = os.path.join(tmp, "wd.ctrw")
     write_model(path, args.rows_per_field)
     C = args.candidates
-    reqs_per_step = max(1, args.ref_requests_per_step)
+    # a bounded sample of the step: the step is 64 requests, the CPU scores ~40 requests/s
+    reqs_per_step = max(1, min(args.ref_requests_per_step, 3000 // max(args.steps, 1)))
     t_build = time.perf_counter()
     import psutil
     from oracle import cpu_baseline as cb, model as om
@@ -188,14 +238,13 @@ def run_reference(args, rank, world):
             client.process_a_request(ids, wts)
     dt = time.perf_counter() - t0
     value = args.steps * reqs_per_step * C / dt
-    sample = "%d requests of %d candidates per step, P=2 shards, protobuf wire encode/decode + fp32 forward + merge + sort; %s; table build %.1fs untimed" % (
-        reqs_per_step, C, client.server.table_note, t_build)
+    sample = "%d of the step's %d requests of %d candidates per step (%d requests timed), P=2 shards, protobuf wire encode/decode + fp32 forward + merge + sort; %s; table build %.1fs untimed" % (
+        reqs_per_step, args.requests_per_step, C, reqs_per_step * args.steps, client.server.table_note, t_build)
     line = {
         "impl": "reference", "metric": "candidates scored/sec", "value": value, "unit": "candidates/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "wide_deep criteo 13 dense + 26 sparse dim16, 10k-candidate requests (BASELINE config 2)",
-                   "candidates_per_request": C, "requests_per_step": reqs_per_step, "rows_per_field": args.rows_per_field},
+        "config": workload_config(args, max(world, 1)),
         "cpu_baseline": {"value": value, "unit": "candidates/s", "cores": client.cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "candidates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -203,6 +252,59 @@ def run_reference(args, rank, world):
     }
     client.close()
     print(json.dumps(line))
+
+
+def sharded_request(n_dev: int, tmp: str):
+    """ONE engine over all N GPUs (what the Java client would hold): processARequest's fan-out (DCNClient.java:146-164)
+    inside the engine.  Reports request latency and whether the scores are the bits a 1-GPU engine gives."""
+    from dtfs_b200 import binding
+    from oracle_free_inputs import criteo_inputs
+    rpf = 1 << 20
+    out = {"n_devices": n_dev, "rows_per_field": rpf,
+           "what": "rank 0 opens ONE engine over all %d GPUs, min_shard_candidates = 1 (always cut N ways, DC:148); sequential requests "
+                   "through ctr_predict from pinned buffers; bit_identical_to_1gpu compares with a single-device engine on the same inputs" % n_dev}
+
+    def lat(eng, ids, wts, n_req):
+        n = ids.shape[0]
+        pi, pw, po = eng.pinned(ids.shape, np.int64), eng.pinned(wts.shape, np.float32), eng.pinned((n,), np.float32)
+        pi.array[:] = ids
+        pw.array[:] = wts
+        ts = []
+        for _ in range(n_req + 20):
+            t0 = time.perf_counter()
+            eng.predict(pi.array, pw.array, out=po.array)
+            ts.append((time.perf_counter() - t0) * 1e3)
+        ts = np.sort(np.array(ts[20:]))
+        res = po.array.copy()
+        for b in (pi, pw, po):
+            b.free()
+        return res, {"p50_ms": float(np.percentile(ts, 50)), "p99_ms": float(np.percentile(ts, 99)), "n": int(ts.size),
+                     "candidates_per_s": float(n / (np.percentile(ts, 50) * 1e-3))}
+
+    cases = [("config3_deepfm_100k", "deepfm", 100000, binding.TABLES_REPLICATED, 200),
+             ("wide_deep_10k", "wide_deep", 10000, binding.TABLES_REPLICATED, 500),
+             ("wide_deep_10k_row_sharded", "wide_deep", 10000, binding.TABLES_ROW_SHARDED, 500)]
+    devs = tuple(range(n_dev))
+    for name, model, C, mode, n_req in cases:
+        try:
+            wpath = os.path.join(tmp, "sh_%s.ctrw" % model)
+            if not os.path.exists(wpath):
+                write_model(wpath, rpf, model=model)
+            ids, wts = criteo_inputs(C, rpf, seed=99)
+            cap = C // n_dev + n_dev + 1
+            with binding.Engine(device_ids=devs, max_candidates=cap, workers_per_device=2, shard_mode=mode, min_shard_candidates=1) as eng:
+                eng.load_weights(wpath)
+                got, l = lat(eng, ids, wts, n_req)
+            with binding.Engine(device_ids=(0,), max_candidates=C, workers_per_device=2) as one:
+                one.load_weights(wpath)
+                ref, l1 = lat(one, ids, wts, max(50, n_req // 4))
+            l["bit_identical_to_1gpu"] = bool(np.array_equal(got, ref))
+            l["one_gpu_p50_ms"] = l1["p50_ms"]
+            l["tables"] = "row-sharded (row mod N), remote rows over NVLink peer loads" if mode == binding.TABLES_ROW_SHARDED else "replicated"
+            out[name] = l
+        except Exception as ex:  # noqa: BLE001
+            out[name] = {"error": repr(ex)}
+    return out
 
 
 def main():
@@ -213,15 +315,18 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--candidates", type=int, default=10000)
     ap.add_argument("--requests-per-step", type=int, default=64)
-    ap.add_argument("--ref-requests-per-step", type=int, default=2)
+    ap.add_argument("--ref-requests-per-step", type=int, default=20, help="reference arm: requests timed per step (a bounded sample of the step)")
     ap.add_argument("--rows-per-field", type=int, default=1 << 22)
-    ap.add_argument("--workers", type=int, default=6, help="host worker threads (one stream each) of the engine: the reference's threadPool")
+    ap.add_argument("--workers", type=int, default=0, help="host worker threads (one stream each) of the engine, the reference's threadPool; "
+                    "0 = 6 (the reference's concurrentNum), fewer when the ranks of a multi-GPU run would oversubscribe the host cores")
     ap.add_argument("--model", default="wide_deep", choices=sorted(MODELS), help="wide_deep is the headline (config 2); others are secondary runs")
     ap.add_argument("--table-dtype", default="fp32", choices=["fp32", "f16"])
     ap.add_argument("--hashed", action="store_true", help="row = mix64(id) & (V-1) (config 4)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--latency-requests", type=int, default=300)
+    ap.add_argument("--closed-loop-requests", type=int, default=10000, help="timed requests of the 6-client closed-loop latency leg (0 = skip)")
+    ap.add_argument("--no-sharded-request", action="store_true", help="N > 1: skip rank 0's one-engine-over-all-GPUs leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -240,9 +345,16 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the engine has no CPU path")
     torch.cuda.set_device(local_rank)
+    # stdout carries exactly one JSON line: everything else that would land there (NCCL_DEBUG=INFO lines, library
+    # chatter) is sent to stderr, where it stays visible to whoever runs this
+    json_out = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
+    if args.workers <= 0:
+        cores = os.cpu_count() or 8
+        args.workers = 6 if world == 1 else max(2, min(6, cores // world - 1))
     dist = None
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"          # keep stdout to the one JSON line
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -312,14 +424,19 @@ def main():
     if stage_ms["tower"] > 0:
         flop = model_flop_per_candidate(args.model)
         a = flop * chunk_rows / (stage_ms["tower"] * 1e-3) / 1e12
-        rl.append({"kernel": "tower_chain_kernel (624->1024->512->256->1 in one launch)", "bound": "tensor", "achieved": a,
-                   "peak": peaks["tc_sustained"], "unit": "TFLOP/s", "frac": a / peaks["tc_sustained"],
-                   "traffic": (per_cand("tower_chain_kernel") or 0) * chunk_rows or None, "ms": stage_ms["tower"], "algorithmic_flop_per_candidate": flop,
-                   "frac_of_burst_peak": a / peaks["tc_burst"]})
+        capped = "sw_power_cap" in (clk.get("reasons") or [])
+        pk = peaks["tc_sustained"] if capped else peaks["tc_burst"]
+        rl.append({"kernel": "tower_chain_kernel (%s in one launch)" % tower_name(args.model), "bound": "tensor", "achieved": a,
+                   "peak": pk, "unit": "TFLOP/s", "frac": a / pk,
+                   "peak_is": "bf16_tflops_sustained (the clock record of this run shows sw_power_cap)" if capped else "bf16_tflops (burst: no power cap in this run's clock record)",
+                   "traffic": ((per_cand("tower_chain_kernel") or 0) * chunk_rows or None) if args.model == "wide_deep" else None, "ms": stage_ms["tower"],
+                   "algorithmic_flop_per_candidate": flop,
+                   "frac_of_burst_peak": a / peaks["tc_burst"], "frac_of_sustained_peak": a / peaks["tc_sustained"],
+                   "note": "with 2 engine streams the next chunk's gather runs beside this kernel: its time here includes that contention"})
     dominant = max(rl, key=lambda r: r["ms"]) if rl else None
     if dominant is not None:
         dominant = dict(dominant)
-        dominant["peak_source"] = "%s (MEASURED_PEAKS.json %s)" % ("hbm_gbs" if dominant["bound"] == "hbm" else "bf16_tflops_sustained", peaks["src"])
+        dominant["peak_source"] = "%s (MEASURED_PEAKS.json %s)" % ("hbm_gbs" if dominant["bound"] == "hbm" else dominant.get("peak_is", "bf16_tflops"), peaks["src"])
         dominant["launch_rows"] = chunk_rows
 
     # ---------------- end to end through the host C ABI (e2e) ----------------
@@ -348,7 +465,9 @@ def main():
         t_e2e = max_over_ranks(time.perf_counter() - t0)
         e2e = {"value": world * n * args.steps / t_e2e, "unit": "candidates/s", "h2d_bytes_per_step": n * F * 12,
                "d2h_bytes_per_step": n * 4, "ms_per_step": t_e2e / args.steps * 1e3,
-               "how": "R ctr_predict_async + ctr_wait per step from pinned host buffers, %d worker streams" % args.workers}
+               "h2d_gbs_per_gpu": n * F * 12 * args.steps / t_e2e / 1e9,
+               "how": "R ctr_predict_async + ctr_wait per step from pinned host buffers (the reference's layout: int64 id + float weight per "
+                      "field slot, 468 B per candidate over the host link), %d worker streams per GPU" % args.workers}
         assert np.array_equal(pin_o.array[:C], d_out[:C].cpu().numpy()), "host path and device path disagree"
         # request latency (reference window DC:141 -> DC:198 without the sort): one 10k request at a time
         ts = []
@@ -396,36 +515,92 @@ def main():
         e2e["shared_context"] = {"value": world * n * args.steps / t_sh, "unit": "candidates/s", "h2d_bytes_per_step": n * fk * 12 + R * n_ctx * 12,
                                  "d2h_bytes_per_step": n * 4, "what": "ctr_predict_shared_async: 26 of 39 fields (13 dense + 13 sparse) given once per request, "
                                  "13 per-candidate fields shipped; additive API beside the drop-in one"}
+        # additive API: the narrow marshaller -- uint32 table rows, weights only for the 13 dense fields (208 B per candidate),
+        # alone and combined with the shared context (13 per-candidate sparse fields: 52 B per candidate).  The caller
+        # keeps its features in this layout: the packing below runs once, outside the timed region.
+        def packed_leg(n_ctx_p):
+            lay = eng.packed_layout(n_ctx_p, weighted_fields=range(N_DENSE))
+            fkp = F - n_ctx_p
+            wk = max(0, N_DENSE - n_ctx_p)
+            pin_r = eng.pinned((n, fkp), np.uint32)
+            pin_pw = eng.pinned((max(n * wk, 1),), np.float32)
+            pw_arr = pin_pw.array[:n * wk].reshape(n, wk)
+            ctxs = []
+            for r in range(R):
+                sl = slice(r * C, (r + 1) * C)
+                ids_r, wts_r = h_ids_t[sl].copy(), h_wts_t[sl].copy()
+                ids_r[:, :n_ctx_p] = ids_r[0, :n_ctx_p]               # one user / context per request, as a real request has
+                wts_r[:, :n_ctx_p] = wts_r[0, :n_ctx_p]
+                ci, cw, _, _ = eng.pack_candidates(lay, ids_r, wts_r, rows_out=pin_r.array[sl], wts_out=pw_arr[sl] if wk else None)
+                ctxs.append((ci.copy(), cw.copy()))
+
+            def pstep():
+                tickets = []
+                for r in range(R):
+                    sl = slice(r * C, (r + 1) * C)
+                    t, _ = eng.predict_packed_async(lay, ctxs[r][0], ctxs[r][1], pin_r.array[sl], pw_arr[sl] if wk else np.empty(0, np.float32), out=pin_o.array[sl])
+                    tickets.append(t)
+                for t in tickets:
+                    eng.wait(t)
+            for _ in range(args.warmup):
+                pstep()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                pstep()
+            torch.cuda.synchronize()
+            t_p = max_over_ranks(time.perf_counter() - t0)
+            same = bool(np.array_equal(pin_o.array[:C], d_out[:C].cpu().numpy())) if n_ctx_p == 0 else None
+            pin_r.free()
+            pin_pw.free()
+            return {"value": world * n * args.steps / t_p, "unit": "candidates/s", "h2d_bytes_per_step": n * (fkp * 4 + wk * 4) + R * n_ctx_p * 12,
+                    "d2h_bytes_per_step": n * 4, "bytes_per_candidate": fkp * 4 + wk * 4, "bit_identical_to_drop_in": same}
+        e2e["packed"] = packed_leg(0)
+        e2e["packed"]["what"] = ("ctr_predict_packed_async: uint32 table rows + weights for the 13 dense fields only (208 instead of 468 B per candidate); "
+                                 "additive API, features kept in this layout by the caller")
+        e2e["packed_shared_context"] = packed_leg(26)
+        e2e["packed_shared_context"]["what"] = "the same with 26 of 39 fields given once per request: 13 uint32 rows per candidate"
         for b in (pin_i, pin_w, pin_o, pin_ci, pin_cw):
             b.free()
+        if world == 1 and args.closed_loop_requests > 0 and args.model == "wide_deep":
+            lat["closed_loop_6_clients"] = closed_loop_latency(wpath, args, args.workers)
 
     # ---------------- CPU baseline (rank 0, N=1 only) ----------------
     cpu = None
-    if world == 1 and rank == 0 and not args.no_cpu_baseline:
-        try:
-            sec, cores, note = cpu_restatement(wpath, args.rows_per_field, C, n_requests=4, warmup=1)
-            cpu = {"value": C / sec, "unit": "candidates/s", "cores": cores, "kind": "port",
-                   "sample": "4 sequential requests of %d candidates, P=2 shards, wire encode/decode + fp32 forward + merge + sort; %s" % (C, note)}
-        except Exception as ex:  # noqa: BLE001
-            cpu = {"value": None, "unit": "candidates/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (ex,)}
-
     eng.close()
+    del d_ids, d_wts, d_out
+    torch.cuda.empty_cache()
+    if world == 1 and rank == 0 and not args.no_cpu_baseline:
+        cpu = cpu_baseline_subprocess(args)
+
+    # ---------------- N > 1: one engine over all the GPUs (rank 0; the other ranks wait on the store, GPUs idle) ----------------
+    sharded = None
+    if dist is not None and not args.no_sharded_request:
+        store = dist.distributed_c10d._get_default_store()
+        barrier()
+        if rank == 0:
+            try:
+                sharded = sharded_request(world, tmp)
+            except Exception as ex:  # noqa: BLE001
+                sharded = {"error": repr(ex)}
+            store.set("ctr_sharded_done", "1")
+        else:
+            store.wait(["ctr_sharded_done"])
     if rank == 0:
         line = {
             "metric": "candidates scored/sec", "value": value, "unit": "candidates/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic",
-            "config": {"workload": "wide_deep criteo 13 dense + 26 sparse dim16, 10k-candidate requests (BASELINE config 2)",
-                       "model": args.model, "tower": "624->" + "->".join(map(str, MODELS[args.model]["hidden"])) + "->1" + (" + %d cross layers 624x624" % MODELS[args.model]["n_cross"] if MODELS[args.model]["n_cross"] else ""),
-                       "id_mode": "hashed" if args.hashed else "direct", "candidates_per_request": C, "requests_per_step": R,
-                       "candidates_per_step_per_gpu": n, "table_rows": int(num_rows), "table_dtype": args.table_dtype,
-                       "table_bytes_per_gpu": int(info.table_bytes_per_device), "id_distribution": "uniform",
-                       "l2": "inputs larger than L2 (%.0f MB ids+weights per step; %.1f GB table, random rows)" % (n * F * 12 / 1e6, info.table_bytes_per_device / 1e9),
-                       "parallelism": "candidate-sharded x%d, tables replicated, no collective" % world},
+            "config": workload_config(args, world),
             "roofline": dominant, "rooflines": rl, "stage_ms_first_chunk": stage_ms,
             "cpu_baseline": cpu, "e2e": e2e, "latency": lat, "gpu_launches": int(launches), "clocks": clk,
+            "host": {"cores": os.cpu_count(), "worker_streams_per_gpu": args.workers},
         }
-        print(json.dumps(line))
+        if sharded is not None:
+            line["sharded_request"] = sharded
+        assert int(info.table_bytes_per_device) == line["config"]["table_bytes_per_gpu"]
+        json_out.write(json.dumps(line) + "\n")
+        json_out.flush()
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

@@ -90,7 +90,7 @@ void on_done(void* user, ctr_ticket, int32_t status) {
 
 int main(int argc, char** argv) {
     std::string lib = "libctr_b200.so", weights, out_path;
-    int n_devices = 1, threads = 6, requests = 10000, warmup = 1000, max_size = 65536, min_size = 64;
+    int n_devices = 1, threads = 6, requests = 10000, warmup = 1000, max_size = 65536, min_size = 64, workers = 4;
     long rows_per_field = 1L << 22;
     double load = 0.7;
     for (int i = 1; i < argc; ++i) {
@@ -100,7 +100,7 @@ int main(int argc, char** argv) {
             return argv[++i];
         };
         if (a == "--help") {
-            printf("usage: stream_sweep_host --weights FILE [--lib libctr_b200.so] [--devices 1] [--threads 6]\n"
+            printf("usage: stream_sweep_host --weights FILE [--lib libctr_b200.so] [--devices 1] [--threads 6] [--workers 4]\n"
                    "         [--requests 10000] [--warmup 1000] [--min 64] [--max 65536] [--load 0.7]\n"
                    "         [--rows-per-field 4194304] [--out table.md]\n"
                    "Config 5: closed loop (6 driver threads) and open loop (Poisson arrivals at --load x the\n"
@@ -110,6 +110,7 @@ int main(int argc, char** argv) {
         else if (a == "--lib") lib = next("--lib");
         else if (a == "--devices") n_devices = atoi(next("--devices"));
         else if (a == "--threads") threads = atoi(next("--threads"));
+        else if (a == "--workers") workers = atoi(next("--workers"));
         else if (a == "--requests") requests = atoi(next("--requests"));
         else if (a == "--warmup") warmup = atoi(next("--warmup"));
         else if (a == "--min") min_size = atoi(next("--min"));
@@ -136,7 +137,7 @@ int main(int argc, char** argv) {
     cfg.n_devices = n_devices;
     for (int i = 0; i < n_devices; ++i) cfg.device_ids[i] = i;
     cfg.max_candidates = max_size;
-    cfg.workers_per_device = 4;
+    cfg.workers_per_device = workers;
     ctr_engine* e = nullptr;
     if (api.create(&cfg, &e) != CTR_OK) { fprintf(stderr, "ctr_engine_create: %s\n", api.last_error()); return 1; }
     if (api.load(e, weights.c_str()) != CTR_OK) { fprintf(stderr, "ctr_engine_load_weights: %s\n", api.last_error()); return 1; }
