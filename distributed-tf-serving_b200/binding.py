@@ -25,7 +25,7 @@ EXPORTS = ["ctr_engine_create", "ctr_engine_destroy", "ctr_engine_load_weights",
            "ctr_engine_launch_count", "ctr_engine_set_timing", "ctr_engine_stage_ms", "ctr_debug_read_rows",
            "ctr_debug_gemm", "ctr_debug_gather", "ctr_score_device_static", "ctr_predict_sorted", "ctr_predict_wire",
            "ctr_wire_parse_request", "ctr_wire_build_response", "ctr_predict_shared_async", "ctr_predict_packed_async",
-           "ctr_pack_candidates"]
+           "ctr_pack_candidates", "ctr_score_devices_exchange"]
 
 
 class CtrConfig(C.Structure):
@@ -75,6 +75,7 @@ def load_library() -> C.CDLL:
     lib.ctr_predict_shared_async.argtypes = [vp, vp, vp, i32, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
     lib.ctr_predict_packed_async.argtypes = [vp, C.POINTER(CtrPackedLayout), vp, vp, vp, vp, i64, vp, vp, vp, C.POINTER(i64)]
     lib.ctr_pack_candidates.argtypes = [vp, C.POINTER(CtrPackedLayout), vp, vp, i64, vp, vp, vp, vp]
+    lib.ctr_score_devices_exchange.argtypes = [vp, vp, vp, vp, vp]
     lib.ctr_wait.argtypes = [vp, i64, i32]
     lib.ctr_predict.argtypes = [vp, vp, vp, i64, vp]
     lib.ctr_alloc_pinned.argtypes = [vp, i64, C.POINTER(vp)]
@@ -333,6 +334,15 @@ class Engine:
         """ctr_score_device_static: same as score_device, but the engine allocates nothing; the
         activations live in the library's fixed scratch (<= STATIC_MAX_CANDIDATES per call)."""
         _check(self.lib.ctr_score_device_static(self.handle, device_index, d_ids, d_wts, n_cand, d_scores, stream or None))
+
+    def score_devices_exchange(self, d_ids, d_wts, n_cand, d_scores):
+        """ctr_score_devices_exchange: per-device lists of raw device pointers / counts (row-sharded engine, NCCL all-to-all)."""
+        G = self.n_devices
+        pi = (C.c_void_p * G)(*d_ids)
+        pw = (C.c_void_p * G)(*d_wts)
+        po = (C.c_void_p * G)(*d_scores)
+        pn = (C.c_int64 * G)(*n_cand)
+        _check(self.lib.ctr_score_devices_exchange(self.handle, pi, pw, pn, po))
 
     def launch_count(self) -> int:
         return int(self.lib.ctr_engine_launch_count(self.handle))

@@ -113,7 +113,7 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
     const ModelDesc& m = e->m;
     DeviceModel& dm = dc.model;
     cudaStream_t st = s.stream;
-    const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1;
+    const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1 && !in.table_override;
     const bool compact = !in.reference_layout(m.F);
 
     GatherParams gp;
@@ -127,7 +127,9 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
         gp.ctx_wts[f] = in.ctx_wts[f];
     }
     gp.bulk_ok = ((reinterpret_cast<uintptr_t>(in.ids) | reinterpret_cast<uintptr_t>(in.wts)) & 15) == 0;
-    gp.table = dm.table; gp.num_rows = (uint64_t)m.V; gp.b0 = dm.b0;
+    gp.table = in.table_override ? in.table_override : dm.table;
+    gp.num_rows = in.table_override ? in.rows_override : (uint64_t)m.V;
+    gp.b0 = dm.b0;
     gp.error_flag = s.d_err;
     gp.n_shards = sharded ? e->cfg.n_devices : 1;
     for (int g = 0; g < CTR_MAX_DEVICES; ++g) gp.shard_base[g] = e->shard_base[g];

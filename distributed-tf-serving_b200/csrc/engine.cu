@@ -4,6 +4,7 @@
 //   weight_file.cuh     CTRW0001 reader                               workers.cuh         shard tasks, worker threads, tickets
 //   engine_state.cuh    model / slot / queue / engine structs         debug_hooks.cuh     ctr_debug_* test hooks
 //   device_setup.cuh    table + weight upload, slots, chain plans     static_scratch.cuh  ctr_score_device_static
+//   exchange.cuh / exchange_host.cuh   row-sharded lookup as an NCCL all-to-all (ctr_score_devices_exchange)
 //   this file           the C ABI (include/ctr_engine.h)
 //
 // What this file replaces in the reference (DC = src/main/java/tensorflow/serving/DCNClient.java):
@@ -41,6 +42,7 @@
 
 #include "engine_base.cuh"
 #include "weight_file.cuh"
+#include "exchange.cuh"
 #include "engine_state.cuh"
 #include "device_setup.cuh"
 #include "device_path.cuh"
@@ -556,3 +558,4 @@ double ctr_engine_stage_ms(ctr_engine* e, int32_t device_index, int32_t stage) {
 
 #include "debug_hooks.cuh"
 #include "static_scratch.cuh"
+#include "exchange_host.cuh"

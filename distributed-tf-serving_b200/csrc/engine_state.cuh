@@ -34,6 +34,8 @@ struct InputView {
     uint64_t weighted_mask = ~0ull;
     const int64_t* ctx_ids = nullptr;        // host memory, n_ctx entries
     const float* ctx_wts = nullptr;
+    const uint8_t* table_override = nullptr; // the rows to gather from instead of the device's table (exchange path:
+    uint64_t rows_override = 0;              //   the rows the owners sent back), and how many there are
     bool reference_layout(int F) const { return n_ctx == 0 && id_bytes == 8 && Fk == F && Wk == F && !ids_are_rows; }
     InputView at(int64_t c0) const {         // the same view, starting at candidate c0
         InputView v = *this;
@@ -174,6 +176,7 @@ struct ctr_engine {
     std::atomic<unsigned> next_first_device{0};   // rotation of the first GPU of requests that use fewer than all
     std::atomic<bool> shutting_down{false};
     uint8_t* shard_base[CTR_MAX_DEVICES] = {nullptr};   // row-sharded tables: every device's shard
+    ExchangeState exch;                                  // NCCL all-to-all variant of the row-sharded lookup (exchange.cuh)
 };
 
 namespace {

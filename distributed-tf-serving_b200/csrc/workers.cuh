@@ -122,7 +122,10 @@ void stop_workers(ctr_engine* e) {
     }
 }
 
+void free_exchange(ctr_engine* e);          // exchange_host.cuh
+
 void free_device_state(ctr_engine* e) {
+    free_exchange(e);
     for (auto& dcp : e->devs) {
         DeviceCtx& dc = *dcp;
         for (auto& s : dc.worker_slots) free_slot(*s);

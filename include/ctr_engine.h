@@ -206,6 +206,19 @@ int32_t ctr_free_pinned(ctr_engine* e, void* p);
 int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids, const void* d_wts,
                          int64_t n_cand, void* d_scores, void* stream);
 
+/* ---- row-sharded tables with an NCCL all-to-all (BASELINE config 4; no counterpart in the reference, whose fan-out
+ * DC:148-156 only knows replicated models) ----
+ * For an engine created with CTR_TABLES_ROW_SHARDED over G >= 2 devices.  One call scores a batch on EVERY device of
+ * the engine (array index = device index; n_cand[d] may be 0): per chunk, each device sends the row indices it needs
+ * to their owners (all-to-all #1, 4 bytes per lookup), the owners copy the rows out of their shard at local HBM
+ * speed, the rows travel back (all-to-all #2, 128 / 64 bytes per lookup) and the ordinary gather + tower kernels
+ * score them -- the alternative to ctr_score_device on such an engine, whose gather reads remote rows directly
+ * through NVLink peer mappings.  Same scores, bit for bit.  Blocks until every device is done.  Needs libnccl.so.2
+ * at run time (bound with dlopen; CTR_ERR_STATE if absent).  A shard can be asked for at most twice its even share
+ * of the lookups of a chunk (CTR_ERR_CAPACITY beyond that). */
+int32_t ctr_score_devices_exchange(ctr_engine* e, const void* const* d_ids, const void* const* d_wts, const int64_t* n_cand,
+                                   void* const* d_scores);
+
 /* ---- device-resident scoring without any allocation (no counterpart in the reference) ----
  * Same contract and same results as ctr_score_device, for callers that must not allocate GPU
  * memory or enter the driver's allocator on the request path: processes whose HBM is already

@@ -80,3 +80,48 @@ def test_row_sharded_tables_equal_replicated(binding, weight_file, hashed):
         assert info.table_bytes_per_device * G <= (w.spec.num_rows + G) * 128 + 128 * G
         assert np.array_equal(sharded, one), "row-sharded vs replicated: max |d| = %g" % np.abs(sharded - one).max()
         assert np.abs(one - om.forward(w, ids, wts, "fp64")).max() <= 2e-3
+
+
+@pytest.mark.parametrize("kind_name,table_dtype,id_mode", [("dcn_v2", 0, 1), ("deepfm", 1, 0), ("wide_deep", 0, 0), ("lr", 0, 0)])
+def test_nccl_exchange_equals_replicated_tables(binding, weight_file, kind_name, table_dtype, id_mode):
+    """BASELINE config 4 as the north star words it: rows sharded over the GPUs (row mod G), looked up with an NCCL
+    all-to-all of row indices and a second one of the rows (ctr_score_devices_exchange).  Every device scores its own
+    batch; the scores must be the bits a replicated single-GPU engine gives, and the bits of the peer-load variant."""
+    import torch
+    from oracle import model as om
+    G = _n_gpus()
+    if G < 2:
+        pytest.skip("needs >= 2 GPUs")
+    kind = {"wide_deep": om.WIDE_DEEP, "deepfm": om.DEEPFM, "dcn_v2": om.DCN_V2, "lr": om.LR}[kind_name]
+    hidden = {"wide_deep": (256, 128), "deepfm": (256, 128), "dcn_v2": (256, 128), "lr": ()}[kind_name]
+    w = make_case(kind, hidden=hidden, n_cross=2 if kind == om.DCN_V2 else 0, table_dtype=table_dtype, id_mode=id_mode)
+    path = weight_file(w)
+    sizes = [3001 + 517 * g for g in range(G)]                         # a different, ragged batch on every device
+    sizes[-1] = 0 if G > 2 else sizes[-1]                              # and one device with nothing to score
+    batches = [om.criteo_inputs(max(n, 1), seed=50 + g, rows_per_field=1 << 10) for g, n in enumerate(sizes)]
+    with binding.Engine(device_ids=(0,), max_candidates=16384) as e1:
+        e1.load_weights(path)
+        want = [e1.predict(ids[:n], wts[:n]).copy() if n else np.empty(0, np.float32) for (ids, wts), n in zip(batches, sizes)]
+    with binding.Engine(device_ids=tuple(range(G)), max_candidates=16384, shard_mode=binding.TABLES_ROW_SHARDED) as eg:
+        eg.load_weights(path)
+        bufs = []
+        for g, ((ids, wts), n) in enumerate(zip(batches, sizes)):
+            with torch.cuda.device(g):
+                bufs.append((torch.from_numpy(ids[:max(n, 1)]).cuda(), torch.from_numpy(wts[:max(n, 1)]).cuda(),
+                             torch.full((max(n, 1),), -1.0, dtype=torch.float32, device="cuda")))
+        for g in range(G):
+            torch.cuda.synchronize(g)
+        for rep in range(2):                                           # the second call reuses every exchange buffer
+            eg.score_devices_exchange([b[0].data_ptr() for b in bufs], [b[1].data_ptr() for b in bufs], sizes, [b[2].data_ptr() for b in bufs])
+            for g, n in enumerate(sizes):
+                got = bufs[g][2][:n].cpu().numpy()
+                assert np.array_equal(got, want[g]), "device %d, call %d: max |d| = %g" % (g, rep, np.abs(got - want[g]).max() if n else 0)
+        # the peer-load variant on the same engine: same bits
+        for g, n in enumerate(sizes):
+            if n:
+                o = torch.empty(n, dtype=torch.float32, device="cuda:%d" % g)
+                eg.score_device(bufs[g][0].data_ptr(), bufs[g][1].data_ptr(), n, o.data_ptr(), device_index=g)
+                assert np.array_equal(o.cpu().numpy(), want[g])
+    ids, wts = batches[0]
+    tol = 1e-5 if kind == om.LR else 2e-3
+    assert np.abs(want[0] - om.forward(w, ids[:sizes[0]], wts[:sizes[0]], "fp64")).max() <= tol

@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--model", default="dcn_v2")
     ap.add_argument("--skip-replicated", action="store_true", help="only the row-sharded engine (a 2^30-row fp32 table is 137 GB replicated)")
+    ap.add_argument("--table-dtype", default="fp32", choices=["fp32", "f16"])
     args = ap.parse_args()
     import torch
     import dtfs_b200  # noqa: F401
@@ -34,7 +35,7 @@ def main():
     tmp = tempfile.mkdtemp(prefix="ctr_rs_")
     wpath = os.path.join(tmp, "m.ctrw")
     rpf = ((1 << args.log2_rows) - 14) // bench.N_SPARSE
-    num_rows = bench.write_model(wpath, rpf, model=args.model, hashed=True)
+    num_rows = bench.write_model(wpath, rpf, model=args.model, hashed=True, table_dtype=1 if args.table_dtype == "f16" else 0)
     assert num_rows == 1 << args.log2_rows, num_rows
     n = args.candidates
     out = {}
@@ -65,6 +66,19 @@ def main():
             dt = time.perf_counter() - t0
         out[name] = {"candidates_per_s": G * n * args.steps / dt, "table_bytes_per_gpu": int(info.table_bytes_per_device),
                      "scores_head": bufs[0][2][:4].cpu().numpy().tolist()}
+        if mode == binding.TABLES_ROW_SHARDED:
+            # the same batches through the NCCL all-to-all variant (one host call drives all the devices)
+            import time
+            args_x = ([b[0].data_ptr() for b in bufs], [b[1].data_ptr() for b in bufs], [n] * G, [b[2].data_ptr() for b in bufs])
+            keep = [b[2].clone() for b in bufs]
+            for _ in range(2):
+                eng.score_devices_exchange(*args_x)
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                eng.score_devices_exchange(*args_x)
+            dt = time.perf_counter() - t0
+            out["row_sharded_nccl_exchange"] = {"candidates_per_s": G * n * args.steps / dt,
+                                                "same_bits_as_peer_loads": all(bool(torch.equal(k, b[2])) for k, b in zip(keep, bufs))}
         eng.close()
     out["gpus"] = G
     out["rows"] = num_rows
