@@ -91,13 +91,16 @@ int32_t ctr_engine_create(const ctr_config* cfg, ctr_engine** out) {
         dc->model.dev = -1;
         e->devs.push_back(std::move(dc));
     }
-    if (cfg->shard_mode == CTR_TABLES_ROW_SHARDED && cfg->n_devices > 1) {
+    if (cfg->n_devices > 1) {       // peer access: row-sharded tables need it; replicated engines use it for the device-side merge
         for (int i = 0; i < cfg->n_devices; ++i)
             for (int j = 0; j < cfg->n_devices; ++j) {
                 if (i == j) continue;
                 int can = 0;
                 CUDA_TRY(cudaDeviceCanAccessPeer(&can, cfg->device_ids[i], cfg->device_ids[j]));
-                if (!can) return fail(CTR_ERR_CUDA, "row-sharded tables need peer access between all devices");
+                if (!can) {
+                    if (cfg->shard_mode == CTR_TABLES_ROW_SHARDED) return fail(CTR_ERR_CUDA, "row-sharded tables need peer access between all devices");
+                    continue;               // replicated tables: peer copies then go through the host, nothing else changes
+                }
                 CUDA_TRY(cudaSetDevice(cfg->device_ids[i]));
                 cudaError_t pe = cudaDeviceEnablePeerAccess(cfg->device_ids[j], 0);
                 if (pe != cudaSuccess && pe != cudaErrorPeerAccessAlreadyEnabled) CUDA_TRY(pe);
@@ -168,6 +171,14 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
         }
         CUDA_TRY(cudaDeviceSynchronize());
     }
+    if (e->cfg.n_devices > 1) {             // merge + sort buffers of multi-GPU sorted requests, on the first GPU
+        DeviceCtx& d0 = *e->devs[0];
+        const int64_t cap = (int64_t)e->cfg.max_candidates * e->cfg.n_devices;
+        CUDA_TRY(cudaSetDevice(d0.model.dev));
+        CUDA_TRY(cudaMalloc(&d0.srt_scores, (size_t)cap * sizeof(float)));
+        if ((rc = alloc_sort_bufs(d0.srt, cap)) != CTR_OK) return rc;
+        d0.sort_cap = cap;
+    }
     e->loaded = true;
     for (int i = 0; i < e->cfg.n_devices; ++i) {
         DeviceCtx& dc = *e->devs[i];
@@ -209,7 +220,8 @@ static int32_t make_compact_view(ctr_engine* e, const char* who, int32_t n_ctx, 
 // The request itself (processARequest, DC:137-203): cut the candidates of the host-side view `in` over the
 // devices, queue one shard task per device, hand back a ticket.
 static int32_t submit_request(ctr_engine* e, const char* who, const InputView& in, int64_t n_cand, float* scores_out, ctr_callback cb,
-                              void* user, ctr_ticket* ticket, bool want_sort = false, int32_t* order_out = nullptr, bool* sorted = nullptr) {
+                              void* user, ctr_ticket* ticket, bool want_sort = false, int32_t* order_out = nullptr, bool* sorted = nullptr,
+                              float* d_merge = nullptr) {
     if (!e || !ticket) return fail(CTR_ERR_INVALID, std::string(who) + ": null argument");
     if (!e->loaded || e->shutting_down) return fail(CTR_ERR_STATE, std::string(who) + ": weights not loaded or engine shutting down");
     if (n_cand < 0 || (n_cand > 0 && (!in.ids || (in.Wk > 0 && !in.wts) || !scores_out))) return fail(CTR_ERR_INVALID, std::string(who) + ": null buffer or negative count");
@@ -254,6 +266,7 @@ static int32_t submit_request(ctr_engine* e, const char* who, const InputView& i
         Task t;
         t.req = req; t.in = in.at(b[i]); t.n = en[i] - b[i]; t.scores = scores_out + b[i];
         t.sort = sort_in_stream; t.order_out = order_out;
+        if (want_sort && !sort_in_stream) t.d_merge = d_merge ? d_merge + b[i] : nullptr;   // ordered merge on GPU 0 (DC:161-164)
         DeviceCtx& dc = *e->devs[(first + i) % G];
         {
             std::lock_guard<std::mutex> lk(dc.q_mu);
@@ -370,30 +383,35 @@ int32_t ctr_predict_sorted(ctr_engine* e, const int64_t* ids, const float* wts, 
                            int32_t* order_out) {
     if (!e || (n_cand > 0 && !sorted_scores_out)) return fail(CTR_ERR_INVALID, "ctr_predict_sorted: null argument");
     if (n_cand > INT32_MAX / 2) return fail(CTR_ERR_CAPACITY, "ctr_predict_sorted: too many candidates");
-    // One shard (one GPU, or a request below the fan-out threshold): scored and sorted on the same stream,
-    // one round trip.  Several shards: ordered merge on the host first (DC:161-164), then the sort on GPU 0.
+    // One shard (one GPU, or a request below the fan-out threshold): scored and sorted on the same stream, one
+    // round trip.  Several shards: every shard copies its scores over NVLink into its slice of one buffer on the
+    // engine's first GPU (the ordered merge of DC:161-164, on the device), which sorts them; one copy back.
+    DeviceCtx& dc = *e->devs[0];
+    const bool multi = e->loaded && e->cfg.n_devices > 1 && dc.sort_cap >= n_cand;
+    std::unique_lock<std::mutex> lk(dc.sort_mu, std::defer_lock);
+    if (multi) lk.lock();                    // the merge buffer is one per engine: multi-GPU sorted requests take turns
     ctr_ticket tk;
     bool sorted = false;
     int32_t rc = submit_request(e, "ctr_predict_sorted", reference_view(ids, wts, e->m.F), n_cand, sorted_scores_out, nullptr, nullptr, &tk,
-                                true, order_out, &sorted);
+                                true, order_out, &sorted, multi ? dc.srt_scores : nullptr);
     if (rc != CTR_OK) return rc;
     rc = ctr_wait(e, tk, -1);
     if (rc != CTR_OK || n_cand == 0 || sorted) return rc;
-    DeviceCtx& dc = *e->devs[0];
-    std::lock_guard<std::mutex> lk(dc.sort_mu);
+    if (!multi) lk.lock();
     CUDA_TRY(cudaSetDevice(dc.model.dev));
     const int n = (int)n_cand;
-    if (dc.sort_cap < n_cand) {
-        const int64_t cap = std::max<int64_t>(n_cand, e->cfg.max_candidates * (int64_t)e->cfg.n_devices);
-        cudaFree(dc.srt_scores);
-        dc.srt_scores = nullptr;
-        dc.sort_cap = 0;
-        CUDA_TRY(cudaMalloc(&dc.srt_scores, cap * sizeof(float)));
-        if ((rc = alloc_sort_bufs(dc.srt, cap)) != CTR_OK) return rc;
-        dc.sort_cap = cap;
-    }
     cudaStream_t st = dc.main_stream;
-    CUDA_TRY(cudaMemcpyAsync(dc.srt_scores, sorted_scores_out, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (!multi) {                            // a request beyond what was sized at load: merged on the host, sorted here
+        if (dc.sort_cap < n_cand) {
+            cudaFree(dc.srt_scores);
+            dc.srt_scores = nullptr;
+            dc.sort_cap = 0;
+            CUDA_TRY(cudaMalloc(&dc.srt_scores, (size_t)n_cand * sizeof(float)));
+            if ((rc = alloc_sort_bufs(dc.srt, n_cand)) != CTR_OK) return rc;
+            dc.sort_cap = n_cand;
+        }
+        CUDA_TRY(cudaMemcpyAsync(dc.srt_scores, sorted_scores_out, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, st));
+    }
     const int32_t* d_order = nullptr;
     if ((rc = launch_sort(e, dc.model, dc.srt, dc.srt_scores, n, st, &d_order)) != CTR_OK) return rc;
     CUDA_TRY(cudaMemcpyAsync(sorted_scores_out, dc.srt.sorted, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, st));

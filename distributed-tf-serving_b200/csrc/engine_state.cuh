@@ -119,6 +119,7 @@ struct Task {
     // A6 (DC:195) on the shard's own stream: scores come back sorted, order_out (may be null) gets the
     // candidate index of each.  Only set on requests that run as ONE shard.
     bool sort = false; int32_t* order_out = nullptr;
+    float* d_merge = nullptr;     // a multi-shard sorted request: this shard's slice of the merge buffer on the engine's first GPU
     bool stop = false;
 };
 

@@ -63,7 +63,11 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
             d_result = s.srt.sorted;
             if (t.order_out) CUDA_TRY(cudaMemcpyAsync(s.h_order, d_order, (size_t)t.n * sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         }
-        CUDA_TRY(cudaMemcpyAsync(dst_scores, d_result, sb, cudaMemcpyDeviceToHost, s.stream));
+        if (t.d_merge) {                                       // ordered merge on the device: straight into GPU 0's buffer
+            CUDA_TRY(cudaMemcpyPeerAsync(t.d_merge, e->devs[0]->model.dev, d_result, s.dev, sb, s.stream));
+        } else {
+            CUDA_TRY(cudaMemcpyAsync(dst_scores, d_result, sb, cudaMemcpyDeviceToHost, s.stream));
+        }
         CUDA_TRY(cudaMemcpyAsync(s.h_err, s.d_err, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         CUDA_TRY(cudaStreamSynchronize(s.stream));
         if (t.sort && t.order_out) memcpy(t.order_out, s.h_order, (size_t)t.n * sizeof(int32_t));
@@ -71,7 +75,7 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
             CUDA_TRY(cudaMemsetAsync(s.d_err, 0, sizeof(int32_t), s.stream));
             return fail(CTR_ERR_INVALID, "feature id out of range for a direct-indexed table");
         }
-        if (!out_pinned) memcpy(t.scores, s.h_scores, sb);
+        if (!out_pinned && !t.d_merge) memcpy(t.scores, s.h_scores, sb);
         return CTR_OK;
     };
     int32_t rc = body();

@@ -10,7 +10,9 @@ METRICS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.
            "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
            "lts__t_sector_hit_rate.pct", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
            "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "launch__grid_size",
-           "launch__block_size", "sm__cycles_elapsed.max", "smsp__cycles_active.avg"]
+           "launch__block_size", "sm__cycles_elapsed.max", "smsp__cycles_active.avg", "sm__inst_executed.avg.per_cycle_elapsed",
+           "smsp__inst_executed.sum", "l1tex__t_sector_hit_rate.pct", "l1tex__m_xbar2l1tex_read_bytes.sum",
+           "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem", "sm__warps_active.avg.per_cycle_active"]
 
 
 def launches(path, out):
@@ -38,10 +40,21 @@ def full(path, out):
         for m in METRICS:
             if m in idx:
                 out.write("   %-66s %s %s\n" % (m, d[idx[m]], units[idx[m]]))
+        stalls = []
+        for h, i in idx.items():
+            if h.startswith("smsp__pcsamp_warps_issue_stalled_") and not h.endswith("_not_issued"):
+                try:
+                    stalls.append((float(d[i]), h[len("smsp__pcsamp_warps_issue_stalled_"):]))
+                except ValueError:
+                    pass
+        tot = sum(v for v, _ in stalls) or 1.0
+        out.write("   warp-state samples: " + ", ".join("%s %.0f%%" % (n, 100 * v / tot) for v, n in sorted(stalls, reverse=True)[:7]) + "\n")
 
 
 if __name__ == "__main__":
     with open(sys.argv[3], "w") as f:
-        launches(sys.argv[1], f)
-        full(sys.argv[2], f)
+        if sys.argv[1] != "-":
+            launches(sys.argv[1], f)
+        for rep in sys.argv[2].split(","):
+            full(rep, f)
     print(open(sys.argv[3]).read())

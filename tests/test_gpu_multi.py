@@ -125,3 +125,24 @@ def test_nccl_exchange_equals_replicated_tables(binding, weight_file, kind_name,
     ids, wts = batches[0]
     tol = 1e-5 if kind == om.LR else 2e-3
     assert np.abs(want[0] - om.forward(w, ids[:sizes[0]], wts[:sizes[0]], "fp64")).max() <= tol
+
+
+def test_sorted_request_over_several_gpus(binding, weight_file):
+    """processARequest including its sort (DCNClient.java:195) when the request is cut over several GPUs: the shards
+    merge their scores in order on the first GPU (peer copies) and the sort runs there -- same result as one GPU."""
+    from oracle import dcn_client as oc, model as om
+    G = _n_gpus()
+    if G < 2:
+        pytest.skip("needs >= 2 GPUs")
+    w = make_case(om.WIDE_DEEP, hidden=(256, 128))
+    path = weight_file(w)
+    with binding.Engine(device_ids=tuple(range(G)), max_candidates=40000, min_shard_candidates=1) as eg:
+        eg.load_weights(path)
+        for n in (G, 10000, 70001):                                      # one candidate per GPU; block sort; multi-block sort
+            ids, wts = om.criteo_inputs(n, seed=n, rows_per_field=1 << 10)
+            base = eg.predict(ids, wts).copy()
+            for _ in range(2):
+                s, idx = eg.predict_sorted(ids, wts)
+                assert np.array_equal(np.sort(idx), np.arange(n))
+                assert np.array_equal(base[idx], s)
+                assert np.array_equal(s, oc.java_float_sort(base))
