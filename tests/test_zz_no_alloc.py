@@ -51,6 +51,16 @@ def test_static_scratch_matches_regular_entry_point(lib_built, weight_file, kind
             assert np.array_equal(got, ref), "call with n=%d: max |d| = %g" % (n, np.abs(got - ref).max())
             # and the ordinary entry point agrees with the oracle, so this is not two wrongs
             assert np.abs(ref - om.forward(w, ids, wts, "fp64")).max() <= 2e-3
+        # and it really allocates nothing: the device's free memory is the same before and after further calls
+        ids, wts = om.criteo_inputs(700, seed=15, rows_per_field=1 << 10)
+        d_ids, d_wts = torch.from_numpy(ids).cuda(), torch.from_numpy(wts).cuda()
+        d_out = torch.empty(700, dtype=torch.float32, device="cuda")
+        torch.cuda.synchronize()
+        free0 = torch.cuda.mem_get_info()[0]
+        for _ in range(3):
+            e.score_device_static(d_ids.data_ptr(), d_wts.data_ptr(), 700, d_out.data_ptr())
+        torch.cuda.synchronize()
+        assert torch.cuda.mem_get_info()[0] == free0
         # a caller-provided stream works the same
         ids, wts = om.criteo_inputs(500, seed=13, rows_per_field=1 << 10)
         st = torch.cuda.Stream()
