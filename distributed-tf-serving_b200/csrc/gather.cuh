@@ -7,24 +7,28 @@
 //     lin[b]   = b0 + sum_f W1[row]*wt           (+ 0.5*sum_k[(sum_f x)^2 - sum_f x^2] for DeepFM)
 //
 // Data layout in HBM ("packed rows"): one table row holds the 16 embedding values AND the
-// first-order weight, so a lookup is ONE place in DRAM and ONE load instruction:
+// first-order weight, so a lookup is ONE place in DRAM (one 128-byte line, fetched once into L1):
 //     fp32 row (128 B): [e0..e15 fp32 | w1 fp32 | pad]      f16 row (64 B): [e0..e15 half | w1 fp32 | pad]
 // B200's DRAM moves 64-byte granules: an fp32 row (68 useful bytes) costs two of them, an f16 row one.
 //
-// Mapping (round 2).  A warp owns "warp tiles" of 4 consecutive candidates and never synchronises with the other
-// warps of its CTA.  Two phases per tile:
-//   expansion  the tile's id / weight lists, staged into the warp's own shared memory with cp.async.bulk (SASS
-//              UBLKCP) on the warp's own mbarrier, are turned into one 8-byte entry {table row, weight} per
-//              (candidate, field): input format, hash, range check and shared context are handled ONCE per id by
-//              one lane, one candidate of the NEXT tile between two candidates of the current one.
-//   gather     4 lanes per row, 8 rows per load instruction: an fp32 row is fetched with ONE 256-bit load per lane
-//              (SASS LDG.E.256: lanes 0-1 the embedding halves, lane 2 the first-order weight), an f16 row with one
-//              128-bit load.  The loads of candidate c+1 are issued slot by slot while candidate c's rows are
-//              consumed out of the same registers (a rolling window of 5-6 loads = 40-48 rows per warp, always
-//              full), so a warp never drains between candidates or tiles.  Inside a candidate the code is straight
-//              line: predicated loads and stores, no branch.
-// Pooling (first-order sum, FM sums) is a fixed per-lane order plus a fixed warp-shuffle tree: the same candidate
-// gets bit-identical results at any position, in any chunk, on any GPU, from any input format.
+// Two kernels, one arithmetic.  Both map a candidate to a warp as lane = g*4 + q: the 8 lane groups g take 8 fields
+// per round, lane q of a group loads embedding values 4q .. 4q+3 of the group's row (128-bit for fp32 rows, 64-bit
+// for f16 rows) and lane 0 the first-order weight; per-lane sums run in field order and the warp reduces with a fixed
+// shuffle tree.  Same lanes, same order, same tree => the same candidate gets bit-identical results at any
+// position, in any chunk, on any GPU, from either kernel (tests/test_gpu_packed.py).
+//   gather_tile_kernel   reference layout.  A CTA stages the lists of a 32-candidate tile with two bulk copies
+//                        (cp.async.bulk, SASS UBLKCP, double buffered), a warp takes a candidate, issues all its row
+//                        loads, then consumes them.
+//   gather_pool_kernel   compact layouts.  A warp owns tiles of 4 candidates and never synchronises with the other
+//                        warps; the tile's lists (bulk copy into the warp's own buffer on its own mbarrier) are first
+//                        EXPANDED into one 8-byte entry {table row, weight} per (candidate, field) -- format, hash,
+//                        range check and shared context handled once per id by one lane, one candidate of the next
+//                        tile between two candidates of the current one -- then gathered with straight-line code
+//                        (predicated loads and stores).  The loop is written as a rolling window (consume slot j of
+//                        candidate c, issue slot j of candidate c+1), but every row load of a loop lands on the same
+//                        hardware scoreboard (tools/sass_scoreboards.py), so waiting for the oldest load waits for the
+//                        newest too and ptxas schedules it as "consume all, issue all": the overlap comes from the 32
+//                        resident warps, not from the window.  DESIGN.md section 3.1 has the measurements.
 //
 // Input formats.  (1) the reference's: ids int64 [n, F], wts float [n, F] (DC:97-108).  (2) compact
 // (kCompact): the first n_ctx fields of every candidate come from one shared list (kernel parameters),
@@ -32,8 +36,8 @@
 // (already hashed by the host packer), and weights only for the fields flagged in weighted_mask (the
 // others are 1.0) -- what ctr_predict_shared_async / ctr_predict_packed_async ship over the host link.
 //
-// Footprint: 256 threads x 64 registers and ~30 KB of shared memory per CTA, so that one CTA fits on an SM
-// NEXT TO the resident tower CTA (tower.cuh) and a chunk's gather runs under the previous chunk's tower.
+// Footprint: 256 threads x 64 registers and <= 30 KB of shared memory per CTA: four CTAs per SM alone, or one beside
+// the resident tower CTA (tower.cuh) when both kernels prefer the largest shared-memory carve-out (device_path.cuh).
 //
 // Roofline: HBM.  Algorithmic bytes per candidate (F=39: 13 dense + 26 sparse, fp32 table):
 // 468 (ids+wts) + 26*(64+4) (rows; the 13 dense-field rows stay in L1/L2) + 4 = 2240 B.
