@@ -100,6 +100,31 @@ int32_t launch_chain(const Chain& c, const Slot& s, int n, float* d_scores, int 
     return CTR_OK;
 }
 
+// Bring-up: CTR_TIMELINE=1 records an event in front of and behind every kernel of a ctr_score_device call (all
+// streams) and prints when each ran, relative to the first one -- which kernels really overlap in time.
+struct TimelineMark { cudaEvent_t ev; const char* what; int slot; };
+static std::vector<TimelineMark> g_timeline;
+static const bool g_timeline_on = getenv("CTR_TIMELINE") != nullptr;
+void timeline_mark(const char* what, int slot, cudaStream_t st) {
+    if (!g_timeline_on || g_timeline.size() >= 256) return;
+    cudaEvent_t ev;
+    if (cudaEventCreate(&ev) != cudaSuccess) return;
+    cudaEventRecord(ev, st);
+    g_timeline.push_back({ev, what, slot});
+}
+void timeline_dump() {
+    if (!g_timeline_on || g_timeline.empty()) return;
+    static int dumps = 0;
+    const bool print = ++dumps == 8;            // one call, after warm-up
+    for (size_t i = 0; i < g_timeline.size(); ++i) {
+        float ms = 0.f;
+        if (print && cudaEventElapsedTime(&ms, g_timeline[0].ev, g_timeline[i].ev) == cudaSuccess)
+            fprintf(stderr, "[timeline] stream %d %-14s %9.1f us\n", g_timeline[i].slot, g_timeline[i].what, ms * 1e3);
+    }
+    for (auto& m : g_timeline) cudaEventDestroy(m.ev);
+    g_timeline.clear();
+}
+
 // Records a CUDA event on the launching stream in front of a stage (stage -2 = end of chunk).
 void mark(ctr_engine* e, Slot& s, int stage) {
     if (!e->timing || !s.time_this || !s.tev || s.sets_recorded >= Slot::kTimeSets || s.cur_mark >= Slot::kTimeMarks) return;
@@ -136,7 +161,10 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
     if (m.kind == CTR_MODEL_LR) { gp.scores = d_scores; }
     else { gp.X = s.buf[0]; gp.ldx = s.ld[0]; gp.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide; }
     mark(e, s, 0);
+    const int tl_slot = (int)(reinterpret_cast<uintptr_t>(st) >> 4 & 0xff);
+    timeline_mark("gather begin", tl_slot, st);
     launch_gather(m, compact, gp, n, dm.num_sms, st);
+    timeline_mark("gather end", tl_slot, st);
     CUDA_TRY(cudaGetLastError());
     e->launches.fetch_add(1, std::memory_order_relaxed);
     int li = 0;
@@ -170,6 +198,7 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
             cudaFree(d_prof);
         }
     }
+    timeline_mark("tower end", tl_slot, st);
     mark(e, s, -2);
     return CTR_OK;
 }

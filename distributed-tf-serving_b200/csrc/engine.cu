@@ -532,6 +532,7 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
         CUDA_TRY(cudaEventRecord(dc.dev_slots[w]->join_ev, dc.dev_slots[w]->stream));
         CUDA_TRY(cudaStreamWaitEvent(origin, dc.dev_slots[w]->join_ev, 0));
     }
+    if (g_timeline_on) { CUDA_TRY(cudaStreamSynchronize(origin)); timeline_dump(); }
     if (!user) {
         CUDA_TRY(cudaStreamSynchronize(origin));
         int32_t err = 0;
