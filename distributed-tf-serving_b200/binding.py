@@ -42,7 +42,7 @@ class CtrModelInfo(C.Structure):
 
 
 class CtrPackedLayout(C.Structure):
-    _fields_ = [("struct_size", C.c_int32), ("n_ctx_fields", C.c_int32), ("weighted_mask", C.c_uint64)]
+    _fields_ = [("struct_size", C.c_int32), ("n_ctx_fields", C.c_int32), ("weighted_mask", C.c_uint64), ("fixed_id_mask", C.c_uint64)]
 
 
 CALLBACK = C.CFUNCTYPE(None, C.c_void_p, C.c_int64, C.c_int32)
@@ -244,27 +244,35 @@ class Engine:
         return t.value, out
 
     @staticmethod
-    def packed_layout(n_ctx_fields: int = 0, weighted_fields=()) -> CtrPackedLayout:
-        """Layout of a packed request: which leading fields are shared context, which fields carry weights."""
+    def packed_layout(n_ctx_fields: int = 0, weighted_fields=(), fixed_id_fields=()) -> CtrPackedLayout:
+        """Layout of a packed request: which leading fields are shared context, which fields carry weights, which
+        per-candidate fields have one id for the whole request (no id column: the id travels once)."""
         lay = CtrPackedLayout()
         lay.struct_size = C.sizeof(CtrPackedLayout)
         lay.n_ctx_fields = n_ctx_fields
         lay.weighted_mask = sum(1 << int(f) for f in weighted_fields)
+        lay.fixed_id_mask = sum(1 << int(f) for f in fixed_id_fields if int(f) >= n_ctx_fields)
         return lay
+
+    def packed_shape(self, layout: CtrPackedLayout):
+        """(id columns, weight columns, fixed ids) per candidate of a layout for the loaded model."""
+        nc = layout.n_ctx_fields
+        cand = ((1 << self.num_fields) - 1) & ~((1 << nc) - 1)
+        n_fixed = bin(layout.fixed_id_mask & cand).count("1")
+        return (self.num_fields - nc - n_fixed, bin(layout.weighted_mask & cand).count("1"), n_fixed)
 
     def pack_candidates(self, layout: CtrPackedLayout, ids, wts, rows_out=None, wts_out=None):
         """ctr_pack_candidates: reference lists [n, F] -> (ctx_ids, ctx_wts, cand_rows uint32 [n, Fk], cand_wts [n, Wk])."""
         ids, wts, n = self._check_inputs(ids, wts)
         nc = layout.n_ctx_fields
-        fk = self.num_fields - nc
-        wk = bin(layout.weighted_mask >> nc & ((1 << fk) - 1)).count("1")
+        fk, wk, n_fixed = self.packed_shape(layout)
         rows = rows_out if rows_out is not None else np.empty((n, fk), np.uint32)
         cw = wts_out if wts_out is not None else np.empty((n, wk), np.float32)
-        ctx_i = np.zeros(max(nc, 1), np.int64)
+        ctx_i = np.zeros(max(nc + n_fixed, 1), np.int64)
         ctx_w = np.zeros(max(nc, 1), np.float32)
         _check(self.lib.ctr_pack_candidates(self.handle, C.byref(layout), ids.ctypes.data, wts.ctypes.data, n, rows.ctypes.data,
                                             cw.ctypes.data if wk else None, ctx_i.ctypes.data, ctx_w.ctypes.data))
-        return ctx_i[:nc], ctx_w[:nc], rows, cw
+        return ctx_i[:nc + n_fixed], ctx_w[:nc], rows, cw
 
     def predict_packed_async(self, layout: CtrPackedLayout, ctx_ids, ctx_wts, cand_rows, cand_wts, out: Optional[np.ndarray] = None):
         """Packed request: uint32 table rows, weights only for the layout's weighted fields, optional shared context."""
@@ -272,13 +280,13 @@ class Engine:
         ctx_wts = np.ascontiguousarray(ctx_wts, np.float32)
         cand_rows = np.asarray(cand_rows)
         cand_wts = np.asarray(cand_wts)
-        fk = self.num_fields - layout.n_ctx_fields
+        fk, _, n_fixed = self.packed_shape(layout)
         if cand_rows.dtype != np.uint32 or not cand_rows.flags.c_contiguous or cand_rows.size % fk:
             raise TypeError("cand_rows must be C-contiguous uint32 [n, %d]" % fk)
         if cand_wts.size and (cand_wts.dtype != np.float32 or not cand_wts.flags.c_contiguous):
             raise TypeError("cand_wts must be C-contiguous float32")
-        if ctx_ids.size != layout.n_ctx_fields or ctx_wts.size != layout.n_ctx_fields:
-            raise ValueError("context lists need n_ctx_fields entries")
+        if ctx_ids.size != layout.n_ctx_fields + n_fixed or ctx_wts.size != layout.n_ctx_fields:
+            raise ValueError("ctx_ids needs n_ctx_fields + fixed-id entries, ctx_wts n_ctx_fields")
         n = cand_rows.size // fk
         if out is None:
             out = np.empty(n, np.float32)

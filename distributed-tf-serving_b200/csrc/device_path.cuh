@@ -146,10 +146,15 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
     gp.ids = in.ids; gp.wts = in.wts; gp.n = n; gp.F = m.F;
     gp.Fk = in.Fk; gp.Wk = in.Wk; gp.id_bytes = in.id_bytes; gp.n_ctx = in.n_ctx; gp.weighted_mask = in.weighted_mask;
     gp.hashed = m.id_mode == CTR_ID_HASHED && !in.ids_are_rows;
-    for (int f = 0; f < in.n_ctx; ++f) {     // context ids always arrive as ids: bring them to what the per-candidate list holds
+    gp.id_mask = in.id_mask;
+    {   // context ids and fixed ids always arrive as ids: bring them to what the per-candidate list holds, indexed by field
         const bool to_row = in.ids_are_rows && m.id_mode == CTR_ID_HASHED;
-        gp.ctx_ids[f] = to_row ? (int64_t)(mix64((uint64_t)in.ctx_ids[f]) & ((uint64_t)m.V - 1)) : in.ctx_ids[f];
-        gp.ctx_wts[f] = in.ctx_wts[f];
+        auto conv = [&](int64_t id) { return to_row ? (int64_t)(mix64((uint64_t)id) & ((uint64_t)m.V - 1)) : id; };
+        for (int f = 0; f < in.n_ctx; ++f) { gp.ctx_ids[f] = conv(in.ctx_ids[f]); gp.ctx_wts[f] = in.ctx_wts[f]; }
+        int k = in.n_ctx;
+        if (compact)
+            for (int f = in.n_ctx; f < m.F; ++f)
+                if (!((in.id_mask >> f) & 1ull)) gp.ctx_ids[f] = conv(in.ctx_ids[k++]);
     }
     gp.bulk_ok = ((reinterpret_cast<uintptr_t>(in.ids) | reinterpret_cast<uintptr_t>(in.wts)) & 15) == 0;
     gp.table = in.table_override ? in.table_override : dm.table;

@@ -201,7 +201,8 @@ int32_t ctr_engine_model_info(ctr_engine* e, ctr_model_info* out) {
 }
 
 // Checks a compact layout against the loaded model and fills the view's derived fields.
-static int32_t make_compact_view(ctr_engine* e, const char* who, int32_t n_ctx, uint64_t weighted_mask, bool narrow_rows, InputView* v) {
+static int32_t make_compact_view(ctr_engine* e, const char* who, int32_t n_ctx, uint64_t weighted_mask, uint64_t fixed_id_mask, bool narrow_rows,
+                                 InputView* v) {
     if (!e) return fail(CTR_ERR_INVALID, std::string(who) + ": null engine");
     if (!e->loaded) return fail(CTR_ERR_STATE, std::string(who) + ": weights not loaded");
     const int F = e->m.F;
@@ -209,7 +210,9 @@ static int32_t make_compact_view(ctr_engine* e, const char* who, int32_t n_ctx, 
     const uint64_t field_bits = F >= 64 ? ~0ull : ((1ull << F) - 1ull);
     const uint64_t cand_bits = field_bits & ~((1ull << n_ctx) - 1ull);
     v->n_ctx = n_ctx;
-    v->Fk = F - n_ctx;
+    v->id_mask = field_bits & ~(fixed_id_mask & cand_bits);
+    v->Fk = __builtin_popcountll(v->id_mask & cand_bits);
+    if (v->Fk < 1) return fail(CTR_ERR_INVALID, std::string(who) + ": at least one field must keep a per-candidate id column");
     v->weighted_mask = weighted_mask & field_bits;
     v->Wk = __builtin_popcountll(weighted_mask & cand_bits);
     v->id_bytes = narrow_rows ? 4 : 8;
@@ -225,7 +228,7 @@ static int32_t submit_request(ctr_engine* e, const char* who, const InputView& i
     if (!e || !ticket) return fail(CTR_ERR_INVALID, std::string(who) + ": null argument");
     if (!e->loaded || e->shutting_down) return fail(CTR_ERR_STATE, std::string(who) + ": weights not loaded or engine shutting down");
     if (n_cand < 0 || (n_cand > 0 && (!in.ids || (in.Wk > 0 && !in.wts) || !scores_out))) return fail(CTR_ERR_INVALID, std::string(who) + ": null buffer or negative count");
-    if (in.n_ctx > 0 && (!in.ctx_ids || !in.ctx_wts)) return fail(CTR_ERR_INVALID, std::string(who) + ": null context list");
+    if ((in.n_ctx > 0 && (!in.ctx_ids || !in.ctx_wts)) || (in.Fk + in.n_ctx < e->m.F && !in.ctx_ids)) return fail(CTR_ERR_INVALID, std::string(who) + ": null context list");
     // How many GPUs this request is cut over.  The reference always cuts hostsList.size() ways (DC:38,
     // DC:148); scores do not depend on the cut, and for a small request the fan-out only costs host
     // work and tail latency (8 GPUs, 64-4096 candidates: p99 0.42-0.5 ms against 0.16 on one GPU), so a
@@ -288,7 +291,7 @@ int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const fl
                                  const int64_t* cand_ids, const float* cand_wts, int64_t n_cand, float* scores_out,
                                  ctr_callback cb, void* user, ctr_ticket* ticket) {
     InputView v;
-    int32_t rc = make_compact_view(e, "ctr_predict_shared_async", n_ctx_fields, ~0ull, false, &v);
+    int32_t rc = make_compact_view(e, "ctr_predict_shared_async", n_ctx_fields, ~0ull, 0, false, &v);
     if (rc != CTR_OK) return rc;
     v.ids = cand_ids; v.wts = cand_wts; v.ctx_ids = ctx_ids; v.ctx_wts = ctx_wts;
     return submit_request(e, "ctr_predict_shared_async", v, n_cand, scores_out, cb, user, ticket);
@@ -297,9 +300,9 @@ int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const fl
 int32_t ctr_predict_packed_async(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ctx_ids, const float* ctx_wts,
                                  const uint32_t* cand_rows, const float* cand_wts, int64_t n_cand, float* scores_out,
                                  ctr_callback cb, void* user, ctr_ticket* ticket) {
-    if (!layout || layout->struct_size != (int32_t)sizeof(ctr_packed_layout)) return fail(CTR_ERR_INVALID, "ctr_predict_packed_async: ctr_packed_layout missing or of the wrong size (ABI)");
+    if (!layout || (layout->struct_size != (int32_t)sizeof(ctr_packed_layout) && layout->struct_size != 16)) return fail(CTR_ERR_INVALID, "ctr_predict_packed_async: ctr_packed_layout missing or of the wrong size (ABI)");
     InputView v;
-    int32_t rc = make_compact_view(e, "ctr_predict_packed_async", layout->n_ctx_fields, layout->weighted_mask, true, &v);
+    int32_t rc = make_compact_view(e, "ctr_predict_packed_async", layout->n_ctx_fields, layout->weighted_mask, layout->struct_size == 16 ? 0 : layout->fixed_id_mask, true, &v);
     if (rc != CTR_OK) return rc;
     if ((uint64_t)e->m.V > 0xFFFFFFFFull) return fail(CTR_ERR_CAPACITY, "ctr_predict_packed_async: the table has more than 2^32 - 1 rows, 32-bit row indices cannot address it");
     v.ids = cand_rows; v.wts = cand_wts; v.ctx_ids = ctx_ids; v.ctx_wts = ctx_wts;
@@ -310,38 +313,50 @@ int32_t ctr_predict_packed_async(ctr_engine* e, const ctr_packed_layout* layout,
 // caller that keeps the reference's lists): pure host code.
 int32_t ctr_pack_candidates(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ids, const float* wts, int64_t n_cand,
                             uint32_t* cand_rows_out, float* cand_wts_out, int64_t* ctx_ids_out, float* ctx_wts_out) {
-    if (!layout || layout->struct_size != (int32_t)sizeof(ctr_packed_layout)) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: ctr_packed_layout missing or of the wrong size (ABI)");
+    if (!layout || (layout->struct_size != (int32_t)sizeof(ctr_packed_layout) && layout->struct_size != 16)) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: ctr_packed_layout missing or of the wrong size (ABI)");
     InputView v;
-    int32_t rc = make_compact_view(e, "ctr_pack_candidates", layout->n_ctx_fields, layout->weighted_mask, true, &v);
+    int32_t rc = make_compact_view(e, "ctr_pack_candidates", layout->n_ctx_fields, layout->weighted_mask, layout->struct_size == 16 ? 0 : layout->fixed_id_mask, true, &v);
     if (rc != CTR_OK) return rc;
     if (n_cand < 0 || (n_cand > 0 && (!ids || !wts || !cand_rows_out || (v.Wk > 0 && !cand_wts_out)))) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: null buffer or negative count");
     if (v.n_ctx > 0 && n_cand > 0 && (!ctx_ids_out || !ctx_wts_out)) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: null context output");
     const ModelDesc& m = e->m;
     if ((uint64_t)m.V > 0xFFFFFFFFull) return fail(CTR_ERR_CAPACITY, "ctr_pack_candidates: the table has more than 2^32 - 1 rows");
     const int F = m.F, nc = v.n_ctx, Fk = v.Fk, Wk = v.Wk;
+    const int n_fixed = (F - nc) - Fk;
+    if ((nc > 0 || n_fixed > 0) && n_cand > 0 && !ctx_ids_out) return fail(CTR_ERR_INVALID, "ctr_pack_candidates: null context output");
     const bool hashed = m.id_mode == CTR_ID_HASHED;
     const uint64_t row_mask = (uint64_t)m.V - 1;
-    int wcol[CTR_MAX_FIELDS];                 // per-candidate field (0-based after the context) of every weight column
-    int nw = 0;
-    for (int j = 0; j < Fk; ++j) if ((v.weighted_mask >> (nc + j)) & 1ull) wcol[nw++] = j;
-    for (int f = 0; f < nc && n_cand > 0; ++f) { ctx_ids_out[f] = ids[f]; ctx_wts_out[f] = wts[f]; }
+    int idf[CTR_MAX_FIELDS], wf[CTR_MAX_FIELDS], fxf[CTR_MAX_FIELDS];        // fields of the id columns / weight columns / fixed ids
+    int ni = 0, nw = 0, nx = 0;
+    for (int f = nc; f < F; ++f) {
+        if ((v.id_mask >> f) & 1ull) idf[ni++] = f; else fxf[nx++] = f;
+        if ((v.weighted_mask >> f) & 1ull) wf[nw++] = f;
+    }
+    if (n_cand > 0) {
+        for (int f = 0; f < nc; ++f) { ctx_ids_out[f] = ids[f]; ctx_wts_out[f] = wts[f]; }
+        for (int k = 0; k < nx; ++k) ctx_ids_out[nc + k] = ids[fxf[k]];
+    }
     for (int64_t b = 0; b < n_cand; ++b) {
         const int64_t* idr = ids + b * F;
         const float* wtr = wts + b * F;
         for (int f = 0; f < nc; ++f)
             if (idr[f] != ids[f] || memcmp(&wtr[f], &wts[f], sizeof(float)) != 0)
                 return fail(CTR_ERR_INVALID, "ctr_pack_candidates: context field " + std::to_string(f) + " of candidate " + std::to_string(b) + " differs from candidate 0");
+        for (int k = 0; k < nx; ++k)
+            if (idr[fxf[k]] != ids[fxf[k]])
+                return fail(CTR_ERR_INVALID, "ctr_pack_candidates: field " + std::to_string(fxf[k]) + " is declared fixed-id but candidate " + std::to_string(b) + " has another id than candidate 0");
         uint32_t* ro = cand_rows_out + b * Fk;
-        for (int j = 0; j < Fk; ++j) {
-            const uint64_t id = (uint64_t)idr[nc + j];
+        for (int k = 0; k < ni; ++k) {
+            const uint64_t id = (uint64_t)idr[idf[k]];
             // a direct id the table cannot hold becomes row 0xFFFFFFFF: the kernel reports it exactly like the reference layout
-            ro[j] = hashed ? (uint32_t)(mix64(id) & row_mask) : (id > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)id);
-            if (!((v.weighted_mask >> (nc + j)) & 1ull) && wtr[nc + j] != 1.0f)
-                return fail(CTR_ERR_INVALID, "ctr_pack_candidates: field " + std::to_string(nc + j) + " of candidate " + std::to_string(b) + " has weight " +
-                                                 std::to_string(wtr[nc + j]) + " but the layout declares it unweighted (1.0)");
+            ro[k] = hashed ? (uint32_t)(mix64(id) & row_mask) : (id > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)id);
         }
+        for (int f = nc; f < F; ++f)
+            if (!((v.weighted_mask >> f) & 1ull) && wtr[f] != 1.0f)
+                return fail(CTR_ERR_INVALID, "ctr_pack_candidates: field " + std::to_string(f) + " of candidate " + std::to_string(b) + " has weight " +
+                                                 std::to_string(wtr[f]) + " but the layout declares it unweighted (1.0)");
         float* wo = cand_wts_out + b * Wk;
-        for (int k = 0; k < Wk; ++k) wo[k] = wtr[nc + wcol[k]];
+        for (int k = 0; k < Wk; ++k) wo[k] = wtr[wf[k]];
     }
     return CTR_OK;
 }

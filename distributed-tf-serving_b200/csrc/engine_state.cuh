@@ -32,7 +32,8 @@ struct InputView {
     int Fk = 0, Wk = 0, id_bytes = 8, n_ctx = 0;
     bool ids_are_rows = false;               // values index the table directly (hashed by the host packer already)
     uint64_t weighted_mask = ~0ull;
-    const int64_t* ctx_ids = nullptr;        // host memory, n_ctx entries
+    uint64_t id_mask = ~0ull;                // bit f: per-candidate field f has an id column (clear: its id is given once, in ctx_ids)
+    const int64_t* ctx_ids = nullptr;        // host memory: n_ctx context ids, then the ids of the fixed-id fields in field order
     const float* ctx_wts = nullptr;
     const uint8_t* table_override = nullptr; // the rows to gather from instead of the device's table (exchange path:
     uint64_t rows_override = 0;              //   the rows the owners sent back), and how many there are

@@ -62,6 +62,7 @@ struct GatherParams {
     int32_t hashed;            // row = mix64(id) & (num_rows - 1); 0 for direct tables and for ids that already are rows
     int32_t bulk_ok;           // ids/wts base pointers are 16-byte aligned -> bulk copies allowed
     uint64_t weighted_mask;    // bit f: per-candidate field f has a weight column (compact input only)
+    uint64_t id_mask;          // bit f: per-candidate field f has an id column; clear: its id is ctx_ids[f] for every candidate
     const uint8_t* table;      // packed rows
     uint64_t num_rows;         // direct mode: bound; hashed mode: power of two
     float b0;
@@ -73,7 +74,8 @@ struct GatherParams {
     // row-sharded tables (rows striped over devices, row mod n_shards): peer base pointers
     int32_t n_shards;
     const uint8_t* shard_base[8];
-    int64_t ctx_ids[48];       // shared context (compact input): ids (or rows) and weights of fields 0 .. n_ctx-1
+    int64_t ctx_ids[48];       // compact input, indexed by field: ids (or rows) of the context fields and of the fixed-id fields;
+                               // ctx_wts: weights of the context fields 0 .. n_ctx-1
     float ctx_wts[48];
 };
 
@@ -353,7 +355,7 @@ gather_pool_kernel(const __grid_constant__ GatherParams p) {
     auto exp_buf = [&](int b) -> uint8_t* { return kCompact ? wbase + raw_bytes + b * exp_bytes : wbase + b * raw_bytes; };
 
     if (kCompact) {
-        for (int f = tid; f < p.n_ctx; f += kGatherThreads) { s_ctx_id[f] = p.ctx_ids[f]; s_ctx_wt[f] = p.ctx_wts[f]; }
+        for (int f = tid; f < F; f += kGatherThreads) { s_ctx_id[f] = p.ctx_ids[f]; s_ctx_wt[f] = p.ctx_wts[f]; }
     }
     if (lane == 0) {
         mbar_init(&full_bar[warp][0], 1);
@@ -404,8 +406,14 @@ gather_pool_kernel(const __grid_constant__ GatherParams p) {
                     id = (uint64_t)s_ctx_id[f];
                     wt = s_ctx_wt[f];
                 } else {
-                    const int j = f - p.n_ctx, col = c * Fk + j;
-                    id = p.id_bytes == 4 ? (uint64_t)reinterpret_cast<const uint32_t*>(raw)[col] : (uint64_t)reinterpret_cast<const int64_t*>(raw)[col];
+                    const int j = f - p.n_ctx;
+                    const uint64_t im = p.id_mask >> p.n_ctx;
+                    if ((im >> j) & 1ull) {
+                        const int col = c * Fk + __popcll(im & ((1ull << j) - 1ull));
+                        id = p.id_bytes == 4 ? (uint64_t)reinterpret_cast<const uint32_t*>(raw)[col] : (uint64_t)reinterpret_cast<const int64_t*>(raw)[col];
+                    } else {
+                        id = (uint64_t)s_ctx_id[f];                  // the same id for every candidate of the request
+                    }
                     const uint64_t m = p.weighted_mask >> p.n_ctx;
                     wt = ((m >> j) & 1ull) ? swt[c * Wk + __popcll(m & ((1ull << j) - 1ull))] : 1.0f;
                 }

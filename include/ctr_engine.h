@@ -133,25 +133,31 @@ int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const fl
  * field costs a 32-bit table ROW index (the id itself for direct tables; mix64(id) & (rows-1), i.e. what the
  * kernel would compute, for hashed ones) and a weight only if the field is flagged in weighted_mask (the
  * others weigh 1.0, as every sparse field of the reference's own inputs does, DC:67-74):
- * 26*4 + 13*8 = 208 bytes per candidate for the Criteo shape.  It composes with the shared context: the
+ * 26*4 + 13*8 = 208 bytes per candidate for the Criteo shape -- and 26*4 + 13*4 = 156 when the dense fields, whose id is
+ * the same for every candidate (only their value changes), are flagged in fixed_id_mask: such a field has no id
+ * column, its id is given once per request behind the context ids.  It composes with the shared context: the
  * first n_ctx_fields are given once (original int64 ids + weights, exactly as for ctr_predict_shared_async)
- * and cand_rows / cand_wts hold only the remaining fields: cand_rows [n_cand, F - n_ctx_fields] uint32,
- * cand_wts [n_cand, Wk] float with Wk = number of flagged fields among the per-candidate ones, in field
- * order (may be NULL when Wk == 0).  Scores are bit-identical to ctr_predict_async on the expanded lists.
+ * and cand_rows / cand_wts hold only the remaining fields: cand_rows [n_cand, Fk] uint32 with Fk = the per-candidate
+ * fields that are not in fixed_id_mask, cand_wts [n_cand, Wk] float with Wk = number of weighted fields among the
+ * per-candidate ones, both in field order (cand_wts may be NULL when Wk == 0).  ctx_ids holds n_ctx_fields context
+ * ids followed by the ids of the fixed-id fields in field order; ctx_wts holds n_ctx_fields weights.  Scores are bit-identical to ctr_predict_async on the expanded lists.
  * Needs a table of at most 2^32 - 1 rows.  Buffers stay owned by the caller until the ticket completes. */
 typedef struct ctr_packed_layout {
     int32_t struct_size;      /* sizeof(ctr_packed_layout) */
     int32_t n_ctx_fields;     /* leading fields given once per request; 0 = none */
     uint64_t weighted_mask;   /* bit f: field f carries a per-candidate weight (bits of context fields are ignored) */
+    uint64_t fixed_id_mask;   /* bit f: per-candidate field f has the same id in every candidate of a request: no id column,
+                               * the id travels once (after the context ids in ctx_ids).  A struct of the first 16 bytes only
+                               * (struct_size 16) means 0 */
 } ctr_packed_layout;
 int32_t ctr_predict_packed_async(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ctx_ids, const float* ctx_wts,
                                  const uint32_t* cand_rows, const float* cand_wts, int64_t n_cand, float* scores_out,
                                  ctr_callback cb, void* user, ctr_ticket* ticket);
 
 /* The packer for callers that hold the reference's lists (ids int64 / wts float, [n_cand, F]; DC:97-108): writes
- * the packed lists ctr_predict_packed_async takes (and the context of candidate 0 into ctx_*_out when
- * layout->n_ctx_fields > 0).  Pure host code.  Fails with CTR_ERR_INVALID if a field the layout declares
- * unweighted has a weight other than 1.0, or a context field differs between candidates -- the packed
+ * the packed lists ctr_predict_packed_async takes (and the context + fixed ids of candidate 0 into ctx_*_out:
+ * ctx_ids_out needs n_ctx_fields + popcount(fixed_id_mask) entries, ctx_wts_out n_ctx_fields).  Pure host code.  Fails with CTR_ERR_INVALID if a field the layout declares
+ * unweighted has a weight other than 1.0, or a context field / a fixed id differs between candidates -- the packed
  * request would not score what the lists say.  Direct ids the table cannot hold are kept recognisable and
  * fail the request itself, as they do in the reference layout. */
 int32_t ctr_pack_candidates(ctr_engine* e, const ctr_packed_layout* layout, const int64_t* ids, const float* wts, int64_t n_cand,

@@ -46,6 +46,15 @@ def test_packed_equals_reference_layout(binding, om, weight_file, kind_name, tab
             t, out = e.predict_packed_async(lay, ctx_i, ctx_w, rows, pw)
             got = e.wait(t)
             assert np.array_equal(got, want), "n=%d: max |d| = %g" % (n, np.abs(got - want).max())
+            # the dense fields' ids are the same for every candidate: flagged fixed-id they travel once, 4 bytes less per field
+            lay2 = e.packed_layout(n_ctx, weighted_fields=range(13), fixed_id_fields=range(13))
+            fk2, wk2, nfx = e.packed_shape(lay2)
+            assert (fk2, wk2, nfx) == (39 - max(n_ctx, 13), max(0, 13 - n_ctx), max(0, 13 - n_ctx))
+            ci2, cw2, rows2, pw2 = e.pack_candidates(lay2, ids, wts)
+            assert rows2.shape == (n, fk2) and ci2.size == n_ctx + nfx
+            assert np.array_equal(rows2, rows[:, rows.shape[1] - fk2:])
+            t, out = e.predict_packed_async(lay2, ci2, cw2, rows2, pw2)
+            assert np.array_equal(e.wait(t), want), "fixed-id layout, n=%d" % n
         tol = 1e-5 if kind == om.LR else 2e-3
         assert np.abs(want - om.forward(w, ids, wts, "fp64")).max() <= tol
     finally:
@@ -92,6 +101,10 @@ def test_pack_candidates_refuses_what_it_cannot_represent(binding, om, weight_fi
             e.pack_candidates(lay2, ids2, wts)
         assert ei.value.code == -1 and "context" in str(ei.value)
         # an id the direct table cannot hold survives packing as an out-of-range row and fails the REQUEST
+        lay3 = e.packed_layout(0, weighted_fields=range(13), fixed_id_fields=(0, 1, 20))
+        with pytest.raises(binding.CtrError) as ei:                  # field 20 is sparse: its id changes from candidate to candidate
+            e.pack_candidates(lay3, ids, wts)
+        assert ei.value.code == -1 and "fixed-id" in str(ei.value)
         ids3 = ids.copy()
         ids3[2, 30] = 1 << 40
         ci, cw, rows, pw = e.pack_candidates(lay, ids3, wts)
