@@ -151,6 +151,7 @@ struct DeviceCtx {
     float* srt_scores = nullptr;
     SortBufs srt;
     std::deque<Task> queue;
+    std::atomic<int> active{0};                       // shard tasks being processed on this device right now (sizes small tower launches)
     std::atomic<int> queued{0};                       // queue.size(), readable without q_mu (workers poll it briefly before sleeping)
     std::mutex q_mu;
     std::condition_variable q_cv;

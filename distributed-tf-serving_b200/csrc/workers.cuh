@@ -78,7 +78,9 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
         if (!out_pinned && !t.d_merge) memcpy(t.scores, s.h_scores, sb);
         return CTR_OK;
     };
+    dc.active.fetch_add(1, std::memory_order_relaxed);
     int32_t rc = body();
+    dc.active.fetch_sub(1, std::memory_order_relaxed);
     complete_shard(e, t.req, rc, rc == CTR_OK ? std::string() : g_last_error);
 }
 

@@ -1,15 +1,9 @@
 set -x
-B="python bench.py --no-e2e --no-cpu-baseline --steps 300 --warmup 5"
 show() { python -c "
 import sys,json
-for l in sys.stdin:
-    if l.startswith('{'):
-        d=json.loads(l); print('value %.1fM ms/step %.3f'%(d['value']/1e6,d['ms_per_step']), {k:round(v*1000,1) for k,v in d['stage_ms_first_chunk'].items()}, d['clocks']['reasons'], d['clocks']['sm_mhz'])
-    elif 'rror' in l or 'Trace' in l: print(l.rstrip())
-"; }
-for rep in 1 2; do
-echo "== default"; $B 2>/dev/null | show
-echo "== 1 tile in flight"; CTR_TOWER_TILES=1 $B 2>/dev/null | show
-echo "== 1 tile in flight + L2 persist"; CTR_TOWER_TILES=1 CTR_L2_PERSIST=1 $B 2>/dev/null | show
-echo "== 1 tile, streams 1"; CTR_TOWER_TILES=1 CTR_DEVICE_STREAMS=1 $B 2>/dev/null | show
-done
+d=json.loads(sys.stdin.read()); e=d['e2e']; l=d['latency']
+print('value %.1fM e2e %.1fM shared %.1fM packed %.1fM packed+shared %.1fM | seq p50 %.3f p99 %.3f sort p50 %.3f | closed loop p50 %.3f p99 %.3f rps %.0f'%(d['value']/1e6,e['value']/1e6,e['shared_context']['value']/1e6,e['packed']['value']/1e6,e['packed_shared_context']['value']/1e6,l['p50_ms'],l['p99_ms'],l['with_sort_p50_ms'],l['closed_loop_6_clients']['p50_ms'],l['closed_loop_6_clients']['p99_ms'],l['closed_loop_6_clients']['requests_per_s']))"; }
+B="python bench.py --no-cpu-baseline --steps 100"
+echo "== adaptive"; $B 2>/dev/null | show
+echo "== forced spread"; CTR_TOWER_SPREAD=1 $B 2>/dev/null | show
+echo "== forced compact"; CTR_TOWER_SPREAD=0 $B 2>/dev/null | show
