@@ -141,7 +141,8 @@ int32_t ctr_predict_shared_async(ctr_engine* e, const int64_t* ctx_ids, const fl
  * fields that are not in fixed_id_mask, cand_wts [n_cand, Wk] float with Wk = number of weighted fields among the
  * per-candidate ones, both in field order (cand_wts may be NULL when Wk == 0).  ctx_ids holds n_ctx_fields context
  * ids followed by the ids of the fixed-id fields in field order; ctx_wts holds n_ctx_fields weights.  Scores are bit-identical to ctr_predict_async on the expanded lists.
- * Needs a table of at most 2^32 - 1 rows.  Buffers stay owned by the caller until the ticket completes. */
+ * Needs a table of at most 2^32 - 1 rows.  Buffers stay owned by the caller until the ticket completes.  A caller that
+ * lays a request out in one slab -- cand_wts starting at the byte where cand_rows ends -- has it shipped as ONE copy. */
 typedef struct ctr_packed_layout {
     int32_t struct_size;      /* sizeof(ctr_packed_layout) */
     int32_t n_ctx_fields;     /* leading fields given once per request; 0 = none */

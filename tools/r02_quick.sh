@@ -2,8 +2,7 @@ set -x
 show() { python -c "
 import sys,json
 d=json.loads(sys.stdin.read()); e=d['e2e']; l=d['latency']
-print('value %.1fM e2e %.1fM shared %.1fM packed %.1fM packed+shared %.1fM | seq p50 %.3f p99 %.3f sort p50 %.3f | closed loop p50 %.3f p99 %.3f rps %.0f'%(d['value']/1e6,e['value']/1e6,e['shared_context']['value']/1e6,e['packed']['value']/1e6,e['packed_shared_context']['value']/1e6,l['p50_ms'],l['p99_ms'],l['with_sort_p50_ms'],l['closed_loop_6_clients']['p50_ms'],l['closed_loop_6_clients']['p99_ms'],l['closed_loop_6_clients']['requests_per_s']))"; }
-B="python bench.py --no-cpu-baseline --steps 100"
-echo "== adaptive"; $B 2>/dev/null | show
-echo "== forced spread"; CTR_TOWER_SPREAD=1 $B 2>/dev/null | show
-echo "== forced compact"; CTR_TOWER_SPREAD=0 $B 2>/dev/null | show
+print('value %.1fM e2e %.1fM shared %.1fM packed %.1fM (same bits %s) packed+shared %.1fM | seq p50 %.3f p99 %.3f'%(d['value']/1e6,e['value']/1e6,e['shared_context']['value']/1e6,e['packed']['value']/1e6,e['packed']['bit_identical_to_drop_in'],e['packed_shared_context']['value']/1e6,l['p50_ms'],l['p99_ms']))"; }
+B="python bench.py --no-cpu-baseline --steps 100 --closed-loop-requests 0"
+timeout 600 python -m pytest tests/test_gpu_packed.py -q -m gpu 2>&1 | tail -2
+$B 2>/dev/null | show
