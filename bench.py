@@ -418,7 +418,7 @@ def main():
     if stage_ms["gather"] > 0:
         gbytes = F * 12 + N_SPARSE * ((EMB * 2 if args.table_dtype == "f16" else EMB * 4) + 4)
         a = gbytes * chunk_rows / (stage_ms["gather"] * 1e-3) / 1e9
-        rl.append({"kernel": "gather_tile_kernel (reference layout; the compact layouts use gather_pool_kernel)", "bound": "hbm", "achieved": a, "peak": peaks["hbm"], "unit": "GB/s",
+        rl.append({"kernel": "gather_tile_kernel", "bound": "hbm", "achieved": a, "peak": peaks["hbm"], "unit": "GB/s",
                    "frac": a / peaks["hbm"], "traffic": ((per_cand("gather_tile_kernel") or 0) * chunk_rows or None) if (args.table_dtype == "fp32" and args.model == "wide_deep") else None, "ms": stage_ms["gather"],
                    "algorithmic_bytes_per_candidate": gbytes})
     if stage_ms["tower"] > 0:

@@ -22,67 +22,48 @@ void prefer_max_carveout(Kern k) {
     done.fetch_or(1ull << dev, std::memory_order_relaxed);
 }
 
-// compact layouts -> warp-tile kernel
-template <int TD, int IT, bool E, bool L, bool FM>
-void launch_compact_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
-    if (gp.n_shards > 1) {
-        prefer_max_carveout(gather_pool_kernel<TD, IT, true, E, L, FM, true>);
-        gather_pool_kernel<TD, IT, true, E, L, FM, true><<<grid, kGatherThreads, smem, st>>>(gp);
-    } else {
-        prefer_max_carveout(gather_pool_kernel<TD, IT, true, E, L, FM, false>);
-        gather_pool_kernel<TD, IT, true, E, L, FM, false><<<grid, kGatherThreads, smem, st>>>(gp);
-    }
+// block-tile kernel: the reference layout (C = false) or a compact layout expanded per tile (C = true)
+template <typename Kern>
+void allow_smem(Kern k, size_t smem) {           // more than the 48 KB a kernel gets without asking (48 fields of int64 ids + weights)
+    if (smem > 48 * 1024 && cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) (void)cudaGetLastError();
 }
-template <int TD, int IT>
-void launch_compact_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
-    switch (kind) {
-        case CTR_MODEL_LR: launch_compact_t<TD, IT, false, true, false>(gp, grid, smem, st); break;
-        case CTR_MODEL_WIDE_DEEP: launch_compact_t<TD, IT, true, true, false>(gp, grid, smem, st); break;
-        case CTR_MODEL_DEEPFM: launch_compact_t<TD, IT, true, true, true>(gp, grid, smem, st); break;
-        default: launch_compact_t<TD, IT, true, false, false>(gp, grid, smem, st); break;
-    }
-}
-
-// reference layout -> block-tile kernel
-template <int TD, bool H, bool E, bool L, bool FM>
+template <int TD, bool H, bool E, bool L, bool FM, bool C>
 void launch_tile_t(const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
     if (gp.n_shards > 1) {
-        prefer_max_carveout(gather_tile_kernel<TD, H, E, L, FM, true>);
-        gather_tile_kernel<TD, H, E, L, FM, true><<<grid, kTileThreads, smem, st>>>(gp);
+        prefer_max_carveout(gather_tile_kernel<TD, H, E, L, FM, true, C>);
+        allow_smem(gather_tile_kernel<TD, H, E, L, FM, true, C>, smem);
+        gather_tile_kernel<TD, H, E, L, FM, true, C><<<grid, kTileThreads, smem, st>>>(gp);
     } else {
-        prefer_max_carveout(gather_tile_kernel<TD, H, E, L, FM, false>);
-        gather_tile_kernel<TD, H, E, L, FM, false><<<grid, kTileThreads, smem, st>>>(gp);
+        prefer_max_carveout(gather_tile_kernel<TD, H, E, L, FM, false, C>);
+        allow_smem(gather_tile_kernel<TD, H, E, L, FM, false, C>, smem);
+        gather_tile_kernel<TD, H, E, L, FM, false, C><<<grid, kTileThreads, smem, st>>>(gp);
     }
 }
-template <int TD, bool H>
+template <int TD, bool H, bool C>
 void launch_tile_kind(int kind, const GatherParams& gp, int grid, size_t smem, cudaStream_t st) {
     switch (kind) {
-        case CTR_MODEL_LR: launch_tile_t<TD, H, false, true, false>(gp, grid, smem, st); break;
-        case CTR_MODEL_WIDE_DEEP: launch_tile_t<TD, H, true, true, false>(gp, grid, smem, st); break;
-        case CTR_MODEL_DEEPFM: launch_tile_t<TD, H, true, true, true>(gp, grid, smem, st); break;
-        default: launch_tile_t<TD, H, true, false, false>(gp, grid, smem, st); break;
+        case CTR_MODEL_LR: launch_tile_t<TD, H, false, true, false, C>(gp, grid, smem, st); break;
+        case CTR_MODEL_WIDE_DEEP: launch_tile_t<TD, H, true, true, false, C>(gp, grid, smem, st); break;
+        case CTR_MODEL_DEEPFM: launch_tile_t<TD, H, true, true, true, C>(gp, grid, smem, st); break;
+        default: launch_tile_t<TD, H, true, false, false, C>(gp, grid, smem, st); break;
     }
 }
 
-// The gather of n candidates on `st`.  Reference layout: block-tile kernel (32-candidate tiles).  Compact layouts:
-// warp-tile kernel (a load instruction covers 8 rows, so F <= 40 takes 5 slots per lane and F <= 48 takes 6).
+// The gather of n candidates on `st`: 32-candidate tiles, min(tiles, 4 x SMs) persistent CTAs.
 void launch_gather(const ModelDesc& m, bool compact, const GatherParams& gp, int n, int num_sms, cudaStream_t st) {
     static const int ctas_per_sm = [] { const char* c = getenv("CTR_GATHER_CTAS"); return c ? atoi(c) : 4; }();
     const bool f32 = m.table_dtype == CTR_TABLE_FP32;
+    const int n_tiles = (n + kGatherTile - 1) / kGatherTile;
+    const int grid = std::max(1, std::min(n_tiles, num_sms * ctas_per_sm));
     if (compact) {
-        const int64_t n_tiles = ((int64_t)n + kWarpTile - 1) / kWarpTile;
-        const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((n_tiles + kGatherWarps - 1) / kGatherWarps, (int64_t)num_sms * ctas_per_sm));
-        const size_t smem = (size_t)kGatherWarps * gather_warp_smem(true, m.F, gp.Fk, gp.Wk, gp.id_bytes);
-        const bool wide = m.F > 40;
-        if (f32) { if (wide) launch_compact_kind<0, 6>(m.kind, gp, grid, smem, st); else launch_compact_kind<0, 5>(m.kind, gp, grid, smem, st); }
-        else { if (wide) launch_compact_kind<1, 6>(m.kind, gp, grid, smem, st); else launch_compact_kind<1, 5>(m.kind, gp, grid, smem, st); }
+        const size_t smem = (size_t)kGatherTile * (2 * ((size_t)gp.Fk * gp.id_bytes + (size_t)gp.Wk * 4) + (size_t)m.F * 8);
+        if (f32) launch_tile_kind<0, false, true>(m.kind, gp, grid, smem, st);
+        else launch_tile_kind<1, false, true>(m.kind, gp, grid, smem, st);
     } else {
-        const int n_tiles = (n + kGatherTile - 1) / kGatherTile;
-        const int grid = std::max(1, std::min(n_tiles, num_sms * ctas_per_sm));
         const size_t smem = (size_t)2 * kGatherTile * m.F * 12;
         const bool hashed = gp.hashed != 0;
-        if (f32) { if (hashed) launch_tile_kind<0, true>(m.kind, gp, grid, smem, st); else launch_tile_kind<0, false>(m.kind, gp, grid, smem, st); }
-        else { if (hashed) launch_tile_kind<1, true>(m.kind, gp, grid, smem, st); else launch_tile_kind<1, false>(m.kind, gp, grid, smem, st); }
+        if (f32) { if (hashed) launch_tile_kind<0, true, false>(m.kind, gp, grid, smem, st); else launch_tile_kind<0, false, false>(m.kind, gp, grid, smem, st); }
+        else { if (hashed) launch_tile_kind<1, true, false>(m.kind, gp, grid, smem, st); else launch_tile_kind<1, false, false>(m.kind, gp, grid, smem, st); }
     }
 }
 

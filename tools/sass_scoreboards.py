@@ -4,7 +4,7 @@ barrier it holds (rd) and the scoreboards an instruction waits for (wait) -- dec
 SASS encoding (bits 105-125 of every 128-bit instruction).  ptxas gives a kernel six scoreboards; loads that share one
 complete together as far as a waiting instruction can tell, which is what decides how many loads are really in flight.
 
-  python tools/sass_scoreboards.py distributed-tf-serving_b200/libctr_b200.so gather_pool_kernelILi0ELi5ELb0ELb1ELb1ELb0E [regex]
+  python tools/sass_scoreboards.py distributed-tf-serving_b200/libctr_b200.so gather_tile_kernelILi0ELb0ELb1ELb1ELb0ELb0ELb0E [regex]
 """
 import re
 import subprocess
