@@ -22,7 +22,7 @@ for _ in range(3):
     lay = e.packed_layout(0, weighted_fields=range(13)); t, _ = e.predict_packed_async(lay, *e.pack_candidates(lay, ids, wts)); e.wait(t)
 e.close()
 PY
-ncu --set full --clock-control none --import-source on -k regex:"sort_block|gather_pool" -s 2 -c 2 -f -o gpurun_out/r02_req python /tmp/req.py > /dev/null 2> gpurun_out/ncu_f3.err
+ncu --set full --clock-control none --import-source on -k regex:"sort_block|gather_tile" -s 2 -c 2 -f -o gpurun_out/r02_req python /tmp/req.py > /dev/null 2> gpurun_out/ncu_f3.err
 tail -2 gpurun_out/ncu_f1.err gpurun_out/ncu_f2.err gpurun_out/ncu_f3.err
 B="python bench.py --no-e2e --no-cpu-baseline --steps 100 --warmup 5"
 for m in deepfm dcn_v2; do $B --model $m > gpurun_out/r02_bench_$m.json 2>/dev/null; done
