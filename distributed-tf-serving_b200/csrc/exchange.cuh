@@ -101,15 +101,18 @@ __global__ void exch_serve_kernel(const uint8_t* table, int row_shift, const uin
     }
 }
 
-// Buffers of one device for the exchange of one chunk.
+// Buffers of one device for the exchange.  What the score stage reads (slot_of_pos, got) exists twice: chunk k+1 is
+// exchanged while chunk k is scored.
 struct ExchangeBufs {
     uint32_t* counts = nullptr;      // [G] lookups this device sends to each owner; then the scatter cursors
     uint32_t* send_rows = nullptr;   // [chunk * F] local row indices, bucket after bucket
-    uint32_t* slot_of_pos = nullptr; // [chunk * F]
+    uint32_t* slot_of_pos[2] = {nullptr, nullptr};   // [chunk * F]
     uint32_t* req_rows = nullptr;    // [cap_req] what the peers ask this device for
     uint8_t* reply = nullptr;        // [cap_req] rows served
-    uint8_t* got = nullptr;          // [chunk * F] rows that came back: the score stage's table
+    uint8_t* got[2] = {nullptr, nullptr};            // [chunk * F] rows that came back: the score stage's table
     uint32_t* h_counts = nullptr;    // pinned [G]
+    cudaEvent_t scored[2] = {nullptr, nullptr};      // the score stage is done with buffer set i
+    cudaEvent_t exchanged = nullptr;                 // the exchange of the current chunk is complete on this device
 };
 
 }  // namespace

@@ -7,7 +7,9 @@ void free_exchange(ctr_engine* e) {
     for (size_t d = 0; d < x.bufs.size(); ++d) {
         cudaSetDevice(e->cfg.device_ids[d]);
         ExchangeBufs& b = x.bufs[d];
-        cudaFree(b.counts); cudaFree(b.send_rows); cudaFree(b.slot_of_pos); cudaFree(b.req_rows); cudaFree(b.reply); cudaFree(b.got);
+        cudaFree(b.counts); cudaFree(b.send_rows); cudaFree(b.req_rows); cudaFree(b.reply);
+        for (int i = 0; i < 2; ++i) { cudaFree(b.slot_of_pos[i]); cudaFree(b.got[i]); if (b.scored[i]) cudaEventDestroy(b.scored[i]); }
+        if (b.exchanged) cudaEventDestroy(b.exchanged);
         cudaFreeHost(b.h_counts);
     }
     x.bufs.clear();
@@ -40,10 +42,14 @@ int32_t setup_exchange(ctr_engine* e) {
         ExchangeBufs& b = x.bufs[d];
         CUDA_TRY(cudaMalloc(&b.counts, CTR_MAX_DEVICES * sizeof(uint32_t)));
         CUDA_TRY(cudaMalloc(&b.send_rows, elems * sizeof(uint32_t)));
-        CUDA_TRY(cudaMalloc(&b.slot_of_pos, elems * sizeof(uint32_t)));
         CUDA_TRY(cudaMalloc(&b.req_rows, x.cap_req * sizeof(uint32_t)));
         CUDA_TRY(cudaMalloc(&b.reply, x.cap_req << shift));
-        CUDA_TRY(cudaMalloc(&b.got, elems << shift));
+        for (int i = 0; i < 2; ++i) {
+            CUDA_TRY(cudaMalloc(&b.slot_of_pos[i], elems * sizeof(uint32_t)));
+            CUDA_TRY(cudaMalloc(&b.got[i], elems << shift));
+            CUDA_TRY(cudaEventCreateWithFlags(&b.scored[i], cudaEventDisableTiming));
+        }
+        CUDA_TRY(cudaEventCreateWithFlags(&b.exchanged, cudaEventDisableTiming));
         CUDA_TRY(cudaMallocHost(&b.h_counts, CTR_MAX_DEVICES * sizeof(uint32_t)));
     }
     x.ready = true;
@@ -79,7 +85,9 @@ extern "C" int32_t ctr_score_devices_exchange(ctr_engine* e, const void* const* 
         CUDA_TRY(cudaMemsetAsync(e->devs[d]->dev_slots[0]->d_err, 0, sizeof(int32_t), e->devs[d]->main_stream));
     }
     uint32_t cnt[CTR_MAX_DEVICES][CTR_MAX_DEVICES];               // cnt[d][p]: lookups device d sends to owner p
-    for (int64_t c0 = 0; c0 < most; c0 += x.chunk) {
+    int64_t chunk_no = 0;
+    for (int64_t c0 = 0; c0 < most; c0 += x.chunk, ++chunk_no) {
+        const int pb = (int)(chunk_no & 1);             // buffer set of this chunk; chunk_no - 2 used it last
         int n_here[CTR_MAX_DEVICES];
         // ---- bucket (count)
         for (int d = 0; d < G; ++d) {
@@ -88,6 +96,7 @@ extern "C" int32_t ctr_score_devices_exchange(ctr_engine* e, const void* const* 
             ExchangeBufs& b = x.bufs[d];
             CUDA_TRY(cudaSetDevice(dc.model.dev));
             cudaStream_t st = dc.main_stream;
+            if (chunk_no >= 2) CUDA_TRY(cudaStreamWaitEvent(st, b.scored[pb], 0));      // its score stage has let go of set pb
             CUDA_TRY(cudaMemsetAsync(b.counts, 0, CTR_MAX_DEVICES * sizeof(uint32_t), st));
             if (n_here[d]) {
                 const int64_t elems = (int64_t)n_here[d] * F;
@@ -119,7 +128,7 @@ extern "C" int32_t ctr_score_devices_exchange(ctr_engine* e, const void* const* 
             memcpy(b.h_counts, off, sizeof(off));
             CUDA_TRY(cudaMemcpyAsync(b.counts, b.h_counts, sizeof(off), cudaMemcpyHostToDevice, st));
             exch_scatter_kernel<<<dc.model.num_sms * 4, 256, 0, st>>>(static_cast<const int64_t*>(d_ids[d]) + c0 * F, (int64_t)n_here[d] * F, (uint64_t)m.V, hashed, G,
-                                                                       b.counts, b.send_rows, b.slot_of_pos);
+                                                                       b.counts, b.send_rows, b.slot_of_pos[pb]);
             CUDA_TRY(cudaGetLastError());
             e->launches.fetch_add(1, std::memory_order_relaxed);
         }
@@ -154,7 +163,7 @@ extern "C" int32_t ctr_score_devices_exchange(ctr_engine* e, const void* const* 
             size_t soff = 0, roff = 0;
             for (int p = 0; p < G; ++p) {
                 if (cnt[p][d]) NCCL_TRY(nc.Send(x.bufs[d].reply + (roff << shift), (size_t)cnt[p][d] << shift, ncclUint8, p, x.comms[d], st));
-                if (cnt[d][p]) NCCL_TRY(nc.Recv(x.bufs[d].got + (soff << shift), (size_t)cnt[d][p] << shift, ncclUint8, p, x.comms[d], st));
+                if (cnt[d][p]) NCCL_TRY(nc.Recv(x.bufs[d].got[pb] + (soff << shift), (size_t)cnt[d][p] << shift, ncclUint8, p, x.comms[d], st));
                 soff += cnt[d][p];
                 roff += cnt[p][d];
             }
@@ -166,18 +175,22 @@ extern "C" int32_t ctr_score_devices_exchange(ctr_engine* e, const void* const* 
             DeviceCtx& dc = *e->devs[d];
             Slot& s = *dc.dev_slots[0];
             CUDA_TRY(cudaSetDevice(dc.model.dev));
-            CUDA_TRY(cudaEventRecord(dc.fork_ev, dc.main_stream));
-            CUDA_TRY(cudaStreamWaitEvent(s.stream, dc.fork_ev, 0));
+            CUDA_TRY(cudaEventRecord(x.bufs[d].exchanged, dc.main_stream));
+            CUDA_TRY(cudaStreamWaitEvent(s.stream, x.bufs[d].exchanged, 0));
             InputView v;
-            v.ids = x.bufs[d].slot_of_pos; v.wts = static_cast<const float*>(d_wts[d]) + c0 * F;
+            v.ids = x.bufs[d].slot_of_pos[pb]; v.wts = static_cast<const float*>(d_wts[d]) + c0 * F;
             v.Fk = F; v.Wk = F; v.id_bytes = 4; v.ids_are_rows = true; v.weighted_mask = ~0ull;
-            v.table_override = x.bufs[d].got; v.rows_override = (uint64_t)n_here[d] * F;
+            v.table_override = x.bufs[d].got[pb]; v.rows_override = (uint64_t)n_here[d] * F;
             s.time_this = false;
             rc = score_chunk(e, dc, s, v, n_here[d], static_cast<float*>(d_scores[d]) + c0);
             if (rc != CTR_OK) return rc;
-            CUDA_TRY(cudaEventRecord(s.join_ev, s.stream));
-            CUDA_TRY(cudaStreamWaitEvent(dc.main_stream, s.join_ev, 0));      // the next chunk's exchange reuses the buffers
+            CUDA_TRY(cudaEventRecord(x.bufs[d].scored[pb], s.stream));       // the exchange of chunk_no + 2 waits for this
         }
+    }
+    for (int d = 0; d < G; ++d) {                                   // everything scored before the call returns
+        DeviceCtx& dc = *e->devs[d];
+        CUDA_TRY(cudaSetDevice(dc.model.dev));
+        CUDA_TRY(cudaStreamSynchronize(dc.dev_slots[0]->stream));
     }
     int32_t err = 0;
     for (int d = 0; d < G; ++d) {
