@@ -9,7 +9,7 @@ A step = one pass of the hot path over one batch: R requests of C candidates eac
 (defaults R=64, C=10 000 -> 640 000 candidates, 300 MB of ids+weights: larger than L2).
 
   value    device-resident: ids/weights already in HBM, one ctr_score_device call per step
-           (the engine coalesces the R requests and walks them in chunks of up to 151 552), CUDA events
+           (the engine coalesces the R requests and walks them in chunks of up to 303 104), CUDA events
   e2e      through the host C ABI (ctr_predict_async / ctr_wait) from pinned host buffers,
            H2D and D2H inside the timed region, R requests in flight per step
   roofline dominant kernel by device time (CUDA events around every kernel of the first chunk
@@ -432,7 +432,7 @@ def main():
                    "traffic": ((per_cand("tower_chain_kernel") or 0) * chunk_rows or None) if args.model == "wide_deep" else None, "ms": stage_ms["tower"],
                    "algorithmic_flop_per_candidate": flop,
                    "frac_of_burst_peak": a / peaks["tc_burst"], "frac_of_sustained_peak": a / peaks["tc_sustained"],
-                   "note": "with 2 engine streams the next chunk's gather runs beside this kernel: its time here includes that contention"})
+                   "note": "one engine stream: kernels run back to back, the event-to-event time is the kernel's own"})
     dominant = max(rl, key=lambda r: r["ms"]) if rl else None
     if dominant is not None:
         dominant = dict(dominant)

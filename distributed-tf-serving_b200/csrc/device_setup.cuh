@@ -350,10 +350,10 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     CUDA_TRY(cudaSetDevice(dm.dev));
     s.cap = e->cfg.max_candidates;
     const int pairs = dm.num_sms / 2;
-    // rows per launch: host-request slots hold one request; device-resident slots default to 8 tiles per CTA pair
-    // (8 x 74 x 256 = 151 552 candidates, X = 194 MB per slot): small enough that the first chunk's gather, the
-    // only one that runs with nothing to hide under, is a small part of a call; CTR_CHUNK_ROWS overrides
-    const int want = host_staging ? (int)s.cap : (e->chunk_rows > 0 ? e->chunk_rows : 8 * pairs * 2 * kBM);
+    // rows per launch: host-request slots hold one request; device-resident slots default to 16 tiles per
+    // CTA pair (16 x 74 x 256 = 303 104 candidates, X = 388 MB; measured 239 / 264 / 278 / 284 / 293 M cand/s
+    // at 1 / 2 / 4 / 8 / 16 tiles per pair in round 1), CTR_CHUNK_ROWS overrides
+    const int want = host_staging ? (int)s.cap : (e->chunk_rows > 0 ? e->chunk_rows : 16 * pairs * 2 * kBM);
     s.x_rows = round_up(std::max(want, 1), 2 * kBM);
     CUDA_TRY(cudaMalloc(&s.d_ids, (size_t)s.cap * m.F * sizeof(int64_t)));
     CUDA_TRY(cudaMalloc(&s.d_wts, (size_t)s.cap * m.F * sizeof(float)));

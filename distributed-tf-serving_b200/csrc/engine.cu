@@ -159,9 +159,11 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
             if ((rc = build_slot_plan(e, dc, *s, true)) != CTR_OK) return rc;
             dc.worker_slots.push_back(std::move(s));
         }
-        // Two streams, chunks alternating between them: chunk k+1's gather (HBM-bound, one 256-thread CTA per SM fits
-        // beside the resident tower CTA) runs UNDER chunk k's tower (tensor-bound) instead of in front of it.
-        int n_dev_slots = 2;
+        // One engine stream by default.  With two (CTR_DEVICE_STREAMS=2) chunks alternate between them and chunk k+1's
+        // gather runs beside chunk k's tower -- the two kernels can share an SM since round 2 (tower.cuh) -- but they
+        // trade time almost one for one (+2 % under a sustained power cap, +3-5 % in short runs),
+        // and a kernel's event-to-event time then includes its neighbour, which blurs the per-kernel roofline figures.
+        int n_dev_slots = 1;
         if (const char* c = getenv("CTR_DEVICE_STREAMS")) { int v = atoi(c); if (v >= 1 && v <= 8) n_dev_slots = v; }
         for (int w = 0; w < n_dev_slots; ++w) {
             std::unique_ptr<Slot> s(new Slot());
