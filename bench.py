@@ -318,7 +318,7 @@ def main():
     ap.add_argument("--ref-requests-per-step", type=int, default=20, help="reference arm: requests timed per step (a bounded sample of the step)")
     ap.add_argument("--rows-per-field", type=int, default=1 << 22)
     ap.add_argument("--workers", type=int, default=0, help="host worker threads (one stream each) of the engine, the reference's threadPool; "
-                    "0 = 6 (the reference's concurrentNum), fewer when the ranks of a multi-GPU run would oversubscribe the host cores")
+                    "0 = the host cores left per rank, at most 12 (the reference's pool has 16, DC:42)")
     ap.add_argument("--model", default="wide_deep", choices=sorted(MODELS), help="wide_deep is the headline (config 2); others are secondary runs")
     ap.add_argument("--table-dtype", default="fp32", choices=["fp32", "f16"])
     ap.add_argument("--hashed", action="store_true", help="row = mix64(id) & (V-1) (config 4)")
@@ -352,7 +352,8 @@ def main():
     os.dup2(2, 1)
     if args.workers <= 0:
         cores = os.cpu_count() or 8
-        args.workers = 6 if world == 1 else max(2, min(6, cores // world - 1))
+        # the reference's pool has 16 threads (DC:42); one per host core that is left, at most 12, at least 2
+        args.workers = max(2, min(12, cores // world - (4 if world == 1 else 1)))
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -458,16 +459,20 @@ def main():
         for _ in range(args.warmup):
             e2e_step()
         barrier()
+        lb0 = eng.link_bytes()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             e2e_step()
         torch.cuda.synchronize()
         t_e2e = max_over_ranks(time.perf_counter() - t0)
-        e2e = {"value": world * n * args.steps / t_e2e, "unit": "candidates/s", "h2d_bytes_per_step": n * F * 12,
-               "d2h_bytes_per_step": n * 4, "ms_per_step": t_e2e / args.steps * 1e3,
-               "h2d_gbs_per_gpu": n * F * 12 * args.steps / t_e2e / 1e9,
+        lb1 = eng.link_bytes()
+        h2d_step, d2h_step = (lb1[0] - lb0[0]) // args.steps, (lb1[1] - lb0[1]) // args.steps      # what the engine really copied
+        e2e = {"value": world * n * args.steps / t_e2e, "unit": "candidates/s", "h2d_bytes_per_step": int(h2d_step),
+               "d2h_bytes_per_step": int(d2h_step), "ms_per_step": t_e2e / args.steps * 1e3,
+               "caller_bytes_per_step": n * F * 12, "h2d_gbs_per_gpu": h2d_step * args.steps / t_e2e / 1e9,
                "how": "R ctr_predict_async + ctr_wait per step from pinned host buffers (the reference's layout: int64 id + float weight per "
-                      "field slot, 468 B per candidate over the host link), %d worker streams per GPU" % args.workers}
+                      "field slot, 468 B per candidate); %d worker streams per GPU; with 8 or more shards in flight the workers narrow their "
+                      "shard on the host before it crosses the link (ctr_config.host_pack = 0)" % args.workers}
         assert np.array_equal(pin_o.array[:C], d_out[:C].cpu().numpy()), "host path and device path disagree"
         # request latency (reference window DC:141 -> DC:198 without the sort): one 10k request at a time
         ts = []

@@ -25,13 +25,13 @@ EXPORTS = ["ctr_engine_create", "ctr_engine_destroy", "ctr_engine_load_weights",
            "ctr_engine_launch_count", "ctr_engine_set_timing", "ctr_engine_stage_ms", "ctr_debug_read_rows",
            "ctr_debug_gemm", "ctr_debug_gather", "ctr_score_device_static", "ctr_predict_sorted", "ctr_predict_wire",
            "ctr_wire_parse_request", "ctr_wire_build_response", "ctr_predict_shared_async", "ctr_predict_packed_async",
-           "ctr_pack_candidates", "ctr_score_devices_exchange"]
+           "ctr_pack_candidates", "ctr_score_devices_exchange", "ctr_engine_h2d_bytes", "ctr_engine_d2h_bytes"]
 
 
 class CtrConfig(C.Structure):
     _fields_ = [("struct_size", C.c_int32), ("n_devices", C.c_int32), ("device_ids", C.c_int32 * CTR_MAX_DEVICES),
                 ("max_candidates", C.c_int32), ("workers_per_device", C.c_int32), ("shard_mode", C.c_int32),
-                ("min_shard_candidates", C.c_int32), ("reserved", C.c_int32 * 7)]
+                ("min_shard_candidates", C.c_int32), ("host_pack", C.c_int32), ("reserved", C.c_int32 * 6)]
 
 
 class CtrModelInfo(C.Structure):
@@ -90,6 +90,9 @@ def load_library() -> C.CDLL:
     lib.ctr_last_error.restype = C.c_char_p
     lib.ctr_engine_launch_count.argtypes = [vp]
     lib.ctr_engine_launch_count.restype = i64
+    for fn in (lib.ctr_engine_h2d_bytes, lib.ctr_engine_d2h_bytes):
+        fn.argtypes = [vp]
+        fn.restype = i64
     lib.ctr_engine_set_timing.argtypes = [vp, i32]
     lib.ctr_engine_stage_ms.argtypes = [vp, i32, i32]
     lib.ctr_engine_stage_ms.restype = C.c_double
@@ -161,7 +164,7 @@ class Engine:
     "channel" per GPU."""
 
     def __init__(self, device_ids=(0,), max_candidates: int = 16384, workers_per_device: int = 0,
-                 shard_mode: int = TABLES_REPLICATED, min_shard_candidates: int = 0):
+                 shard_mode: int = TABLES_REPLICATED, min_shard_candidates: int = 0, host_pack: int = 0):
         self.lib = load_library()
         cfg = CtrConfig()
         cfg.struct_size = C.sizeof(CtrConfig)
@@ -172,6 +175,7 @@ class Engine:
         cfg.workers_per_device = workers_per_device
         cfg.shard_mode = shard_mode
         cfg.min_shard_candidates = min_shard_candidates       # 0: engine default; 1: always cut over all GPUs (DC:148)
+        cfg.host_pack = host_pack                             # 0: narrow drop-in shards on the host when the GPU is busy; 1: never; 2: always
         h = C.c_void_p()
         _check(self.lib.ctr_engine_create(C.byref(cfg), C.byref(h)))
         self.handle = h.value
@@ -354,6 +358,10 @@ class Engine:
 
     def launch_count(self) -> int:
         return int(self.lib.ctr_engine_launch_count(self.handle))
+
+    def link_bytes(self):
+        """(host -> device, device -> host) bytes the request path has copied so far."""
+        return int(self.lib.ctr_engine_h2d_bytes(self.handle)), int(self.lib.ctr_engine_d2h_bytes(self.handle))
 
     def set_timing(self, on: bool):
         _check(self.lib.ctr_engine_set_timing(self.handle, 1 if on else 0))

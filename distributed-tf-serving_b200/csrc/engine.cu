@@ -80,6 +80,8 @@ int32_t ctr_engine_create(const ctr_config* cfg, ctr_engine** out) {
     std::unique_ptr<ctr_engine> e(new ctr_engine());
     e->cfg = *cfg;
     if (e->cfg.workers_per_device <= 0) e->cfg.workers_per_device = 2;
+    e->host_pack = cfg->host_pack;
+    if (const char* c = getenv("CTR_HOST_PACK")) e->host_pack = atoi(c);
     if (const char* c = getenv("CTR_CHUNK_ROWS")) { int v = atoi(c); if (v >= 128) e->chunk_rows = round_up(v, 128); }
     for (int i = 0; i < cfg->n_devices; ++i) {
         std::unique_ptr<DeviceCtx> dc(new DeviceCtx());
@@ -564,6 +566,8 @@ int32_t ctr_score_device(ctr_engine* e, int32_t device_index, const void* d_ids,
 }
 
 int64_t ctr_engine_launch_count(ctr_engine* e) { return e ? e->launches.load() : 0; }
+int64_t ctr_engine_h2d_bytes(ctr_engine* e) { return e ? e->h2d_bytes.load() : 0; }
+int64_t ctr_engine_d2h_bytes(ctr_engine* e) { return e ? e->d2h_bytes.load() : 0; }
 
 int32_t ctr_engine_set_timing(ctr_engine* e, int32_t enabled) {
     if (!e) return fail(CTR_ERR_INVALID, "null engine");

@@ -174,11 +174,14 @@ struct ctr_engine {
     std::deque<ctr_ticket> called_back;     // completed requests that had a callback, oldest first (guarded by t_mu)
     std::atomic<int64_t> next_ticket{1};
     std::atomic<int64_t> launches{0};
+    std::atomic<int64_t> h2d_bytes{0}, d2h_bytes{0};    // request path: bytes that crossed the host link
     std::mutex pin_mu;
     std::map<uintptr_t, size_t> pinned;     // base -> bytes (buffers from ctr_alloc_pinned)
     std::atomic<unsigned> next_first_device{0};   // rotation of the first GPU of requests that use fewer than all
     std::atomic<bool> shutting_down{false};
     uint8_t* shard_base[CTR_MAX_DEVICES] = {nullptr};   // row-sharded tables: every device's shard
+    std::atomic<uint64_t> narrow_weighted{0};            // host narrowing: fields seen with a weight != 1.0 so far (sticky)
+    int host_pack = 0;                                   // cfg.host_pack, CTR_HOST_PACK overrides
     ExchangeState exch;                                  // NCCL all-to-all variant of the row-sharded lookup (exchange.cuh)
 };
 

@@ -32,18 +32,70 @@ void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t st
     }
 }
 
+// Host narrowing of a shard that arrived in the reference's layout (DC:97-108: an int64 id and a float weight per field
+// slot): rows[n, F] uint32 + weights[n, Wk] of the fields in `mask`, written behind each other into `slab`.  The loops are
+// plain and branch-free so that the compiler vectorises them.  Returns the fields that carry a weight != 1.0 but are not
+// in `mask` (the caller adds them and packs again); *wide is set when some id does not fit 32 bits.
+constexpr int kNarrowWhenActive = 8;
+
+uint64_t narrow_reference(const int64_t* ids, const float* wts, int64_t n, int F, uint64_t mask, uint32_t* rows, float* pw, bool* wide) {
+    int wf[CTR_MAX_FIELDS], Wk = 0;
+    for (int f = 0; f < F; ++f) if ((mask >> f) & 1ull) wf[Wk++] = f;
+    uint32_t notone[CTR_MAX_FIELDS] = {0};
+    uint64_t hi = 0;
+    for (int64_t b = 0; b < n; ++b) {
+        const int64_t* idr = ids + b * F;
+        const float* wtr = wts + b * F;
+        uint32_t* ro = rows + b * F;
+        float* wo = pw + b * Wk;
+        for (int f = 0; f < F; ++f) { ro[f] = (uint32_t)idr[f]; hi |= (uint64_t)idr[f]; }
+        for (int f = 0; f < F; ++f) notone[f] |= (uint32_t)(wtr[f] != 1.0f);
+        for (int k = 0; k < Wk; ++k) wo[k] = wtr[wf[k]];
+    }
+    *wide = (hi >> 32) != 0;
+    uint64_t more = 0;
+    for (int f = 0; f < F; ++f) if (notone[f] && !((mask >> f) & 1ull)) more |= 1ull << f;
+    return more;
+}
+
 // sendRequest (DC:91-115) for one shard: stage -> H2D -> kernels -> D2H -> hand back.
 void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
     auto body = [&]() -> int32_t {
         CUDA_TRY(cudaSetDevice(s.dev));
-        const InputView& in = t.in;
+        InputView in = t.in;
+        // Host narrowing (ctr_config.host_pack): a reference-layout shard for a direct-id table becomes uint32 rows +
+        // the weights of the fields that ever had one, packed into this slot's pinned slab -- 208 instead of 468 bytes
+        // per candidate for the Criteo shape, the same kernels and the same bits as ctr_predict_packed_async.  A core
+        // narrows at ~10 GB/s of input (measured: 0.45 ms per 10 000 candidates), the link moves 48 GB/s shared by the
+        // shards in flight: narrowing wins from about 8 concurrent shards on (6 workers: 103 -> 89 M candidates/s end
+        // to end, 12 workers: 103 -> 145 M), so that is where the automatic mode switches it on.
+        const int hp = e->host_pack;
+        if (in.reference_layout(e->m.F) && e->m.id_mode == CTR_ID_DIRECT && hp != 1 && t.n > 0 &&
+            (hp == 2 || dc.active.load(std::memory_order_relaxed) >= kNarrowWhenActive)) {
+            const int F = e->m.F;
+            uint32_t* rows = reinterpret_cast<uint32_t*>(s.h_ids);
+            float* pw = reinterpret_cast<float*>(rows + (size_t)t.n * F);
+            const uint64_t all = F >= 64 ? ~0ull : (1ull << F) - 1ull;
+            for (int attempt = 0; attempt <= F; ++attempt) {
+                const uint64_t mask = e->narrow_weighted.load(std::memory_order_relaxed) & all;
+                bool wide = false;
+                const uint64_t more = narrow_reference(static_cast<const int64_t*>(t.in.ids), t.in.wts, t.n, F, mask, rows, pw, &wide);
+                if (wide) break;                               // an id beyond 32 bits: this shard travels as it is
+                if (more) { e->narrow_weighted.fetch_or(more, std::memory_order_relaxed); continue; }
+                in = InputView();
+                in.ids = rows; in.wts = pw; in.Fk = F; in.Wk = __builtin_popcountll(mask); in.id_bytes = 4;
+                in.ids_are_rows = true; in.weighted_mask = mask;
+                break;
+            }
+        }
         const size_t ib = in.ids_bytes(t.n), wb = in.wts_bytes(t.n), sb = (size_t)t.n * sizeof(float);
         // The feature packer: caller buffers that came from ctr_alloc_pinned are DMA'd in place;
         // pageable ones (a Java heap array, a numpy array) are packed into this slot's pinned slab.
         const void* src_ids = in.ids;
         const float* src_wts = in.wts;
-        if (!is_pinned(e, in.ids, ib)) { memcpy(s.h_ids, in.ids, ib); src_ids = s.h_ids; }
-        if (wb && !is_pinned(e, in.wts, wb)) { memcpy(s.h_wts, in.wts, wb); src_wts = s.h_wts; }
+        const bool in_slab = in.ids == static_cast<const void*>(s.h_ids);          // narrowed above: already in pinned memory
+        if (!in_slab && !is_pinned(e, in.ids, ib)) { memcpy(s.h_ids, in.ids, ib); src_ids = s.h_ids; }
+        if (!in_slab && wb && !is_pinned(e, in.wts, wb)) { memcpy(s.h_wts, in.wts, wb); src_wts = s.h_wts; }
         const bool out_pinned = is_pinned(e, t.scores, sb);
         float* dst_scores = out_pinned ? t.scores : s.h_scores;
         // Whatever the layout (reference, shared context, packed rows), the lists cross the host link as they
@@ -61,6 +113,8 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
             CUDA_TRY(cudaMemcpyAsync(s.d_ids, src_ids, ib, cudaMemcpyHostToDevice, s.stream));
             if (wb) CUDA_TRY(cudaMemcpyAsync(s.d_wts, src_wts, wb, cudaMemcpyHostToDevice, s.stream));
         }
+        e->h2d_bytes.fetch_add((int64_t)(ib + wb), std::memory_order_relaxed);
+        e->d2h_bytes.fetch_add((int64_t)sb + (t.sort && t.order_out ? (int64_t)sb : 0), std::memory_order_relaxed);
         int32_t rc = score_on_slot(e, dc, s, dv, t.n, s.d_scores);
         if (rc != CTR_OK) return rc;
         const float* d_result = s.d_scores;

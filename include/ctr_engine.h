@@ -71,7 +71,15 @@ typedef struct ctr_config {
     int32_t min_shard_candidates; /* a request is spread over floor(n / this) GPUs, at most n_devices, at least 1
                                    * (the starting GPU rotates); 0 = default 1024; 1 = always cut n_devices ways
                                    * as DC:148 does.  Scores do not depend on it. */
-    int32_t reserved[7];
+    int32_t host_pack;            /* the drop-in request path (ctr_predict_async & co. with the reference's int64 id + float
+                                   * weight lists) can narrow a shard on its worker thread before it crosses the host link:
+                                   * uint32 rows + weights only for the fields that ever had one != 1.0 (the packed layout of
+                                   * ctr_predict_packed_async, 208 instead of 468 bytes per candidate for the Criteo shape;
+                                   * direct-id tables only; same scores, bit for bit).  It trades host CPU (~0.45 ms of one core
+                                   * per 10 000 candidates) for link capacity: 0 = when 8 or more shards are in flight on the GPU
+                                   * (needs workers_per_device >= 8; fewer shards share the link faster than a core narrows),
+                                   * 1 = never, 2 = always */
+    int32_t reserved[6];
 } ctr_config;
 
 typedef struct ctr_engine ctr_engine;
@@ -255,6 +263,10 @@ const char* ctr_last_error(void);
 int32_t ctr_abi_version(void);
 /* Kernels launched by this engine since creation (all devices). */
 int64_t ctr_engine_launch_count(ctr_engine* e);
+/* Bytes the request path (ctr_predict* and friends) has copied host -> device / device -> host since creation: what really
+ * crossed the link, after any host narrowing. */
+int64_t ctr_engine_h2d_bytes(ctr_engine* e);
+int64_t ctr_engine_d2h_bytes(ctr_engine* e);
 /* Stage timing.  ctr_engine_set_timing(e, 1) starts (or restarts) an averaging window: each
  * following ctr_score_device call records CUDA events on the launching stream around every
  * kernel of its FIRST chunk (up to 32 calls per window).  After the caller has synchronised,

@@ -47,7 +47,7 @@ public final class CtrEngine implements AutoCloseable {
         lastError = LINKER.downcallHandle(lib.find("ctr_last_error").orElseThrow(), FunctionDescriptor.of(ADDRESS));
         this.fieldNum = fieldNum;
 
-        // ctr_config: int32 struct_size, n_devices, device_ids[8], max_candidates, workers_per_device, shard_mode, min_shard_candidates, reserved[7]
+        // ctr_config: int32 struct_size, n_devices, device_ids[8], max_candidates, workers_per_device, shard_mode, min_shard_candidates, host_pack, reserved[6]
         final int cfgBytes = 4 * (2 + 8 + 3 + 8);
         MemorySegment cfg = arena.allocate(cfgBytes, 4);
         cfg.fill((byte) 0);

@@ -116,3 +116,42 @@ def test_pack_candidates_refuses_what_it_cannot_represent(binding, om, weight_fi
         assert np.array_equal(e.wait(t), e.predict(ids, wts))
     finally:
         e.close()
+
+
+@pytest.mark.parametrize("kind_name,table_dtype", [("wide_deep", 0), ("deepfm", 1), ("lr", 0)])
+def test_host_narrowing_of_the_drop_in_path(binding, om, weight_file, kind_name, table_dtype):
+    """ctr_config.host_pack: the drop-in request (the reference's int64 id + float weight lists) narrowed on the worker
+    thread before it crosses the host link must score what the untouched lists score, bit for bit -- also when a field
+    that so far always weighed 1.0 suddenly carries a weight (the layout grows), and when an id does not fit 32 bits
+    (the shard travels as it is and fails like it always did)."""
+    kind = {"lr": om.LR, "wide_deep": om.WIDE_DEEP, "deepfm": om.DEEPFM}[kind_name]
+    w = make_case(kind, hidden=() if kind == om.LR else (256, 128), table_dtype=table_dtype)
+    path = weight_file(w)
+    plain = binding.Engine(device_ids=(0,), max_candidates=4096, host_pack=1)
+    narrow = binding.Engine(device_ids=(0,), max_candidates=4096, host_pack=2)
+    plain.load_weights(path)
+    narrow.load_weights(path)
+    try:
+        for n, seed in ((1, 1), (777, 2), (4096, 3)):
+            ids, wts = om.criteo_inputs(n, seed=seed, rows_per_field=1 << 10)
+            assert np.array_equal(narrow.predict(ids, wts), plain.predict(ids, wts)), n
+        ids, wts = om.criteo_inputs(1000, seed=4, rows_per_field=1 << 10)
+        wts[17, 30] = 0.25                                            # a sparse field with a weight: the learned layout widens
+        wts[500:, 20] = 2.0
+        want = plain.predict(ids, wts).copy()
+        assert np.array_equal(narrow.predict(ids, wts), want)
+        assert np.array_equal(narrow.predict(ids, wts), want)        # and stays right once widened
+        ids2, wts2 = om.criteo_inputs(1000, seed=5, rows_per_field=1 << 10)
+        assert np.array_equal(narrow.predict(ids2, wts2), plain.predict(ids2, wts2))
+        s_n, i_n = narrow.predict_sorted(ids2, wts2)
+        s_p, i_p = plain.predict_sorted(ids2, wts2)
+        assert np.array_equal(s_n, s_p) and np.array_equal(i_n, i_p)
+        ids[3, 25] = (1 << 40) + 5                                    # beyond 32 bits: out of range for the table, must FAIL, not wrap
+        for e in (plain, narrow):
+            with pytest.raises(binding.CtrError) as ei:
+                e.predict(ids, wts)
+            assert ei.value.code == -1
+        assert np.array_equal(narrow.predict(ids2, wts2), plain.predict(ids2, wts2))
+    finally:
+        plain.close()
+        narrow.close()
