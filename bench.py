@@ -184,6 +184,30 @@ def cpu_baseline_subprocess(args):
         return {"value": None, "unit": "candidates/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (ex,)}
 
 
+def random_row_rate(device_index: int):
+    """Random 128-byte rows per second this GPU's HBM delivers to a kernel that does nothing else
+    (tools/probes/random_rows_probe.cu, run live; 36.2 G rows/s on this pool's B200s for rows of 32 to 128 bytes alike, with
+    16 to 64 warps per SM and 2 to 16 loads in flight per lane: profiles/r02_random_rows_probe.txt).  The gather kernel's time
+    follows the rows it looks up, not the bytes: this is the roofline that bounds it."""
+    exe = os.path.join(ROOT, "tools", "probes", "random_rows_probe")
+    out = {"peak_rows_per_s": 36.2e9, "source": "profiles/r02_random_rows_probe.txt (committed measurement: the probe did not run here)"}
+    if not os.path.exists(exe):
+        return out
+    try:
+        env = dict(os.environ)
+        visible = env.get("CUDA_VISIBLE_DEVICES")
+        env["CUDA_VISIBLE_DEVICES"] = visible.split(",")[device_index] if visible else str(device_index)
+        txt = subprocess.run([exe, "8", "quick"], capture_output=True, text=True, timeout=120, env=env).stdout
+        import re
+        m = re.search(r"([0-9.]+) G rows/s", txt)
+        if m:
+            out = {"peak_rows_per_s": float(m.group(1)) * 1e9,
+                   "source": "tools/probes/random_rows_probe.cu run on this GPU after the timed region: " + " ".join(txt.split())}
+    except Exception as ex:  # noqa: BLE001
+        out["probe_error"] = repr(ex)
+    return out
+
+
 def closed_loop_latency(wpath: str, args, workers: int):
     """p50 / p99 of a 10 000-candidate request under the reference's load shape (DCNClient.java:30-31, :213-224):
     6 closed-loop client threads, 10 000 timed requests after 1 000 warm-up, C++ over the C ABI."""
@@ -577,6 +601,17 @@ def main():
     eng.close()
     del d_ids, d_wts, d_out
     torch.cuda.empty_cache()
+    if rank == 0 and rl and rl[0]["kernel"].startswith("gather"):
+        rr = random_row_rate(local_rank)
+        g = rl[0]
+        rows = N_SPARSE * chunk_rows / (g["ms"] * 1e-3)
+        g["random_rows"] = {"achieved_rows_per_s": rows, "peak_rows_per_s": rr["peak_rows_per_s"], "frac": rows / rr["peak_rows_per_s"],
+                            "what": "table rows fetched from HBM per second (%d per candidate: the sparse fields; the dense fields' rows are cache-resident) "
+                                    "against the rate of a kernel that only fetches random rows; beside them this kernel streams %d B of lists and "
+                                    "%d B of X per candidate" % (N_SPARSE, F * 12, 2 * int(info.d_padded)),
+                            "peak_source": rr["source"]}
+        if "probe_error" in rr:
+            g["random_rows"]["probe_error"] = rr["probe_error"]
     if world == 1 and rank == 0 and not args.no_cpu_baseline:
         cpu = cpu_baseline_subprocess(args)
 

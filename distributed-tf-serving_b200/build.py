@@ -60,7 +60,21 @@ def build_stream_sweep(force: bool = False) -> str:
     return STREAM_SWEEP
 
 
+ROW_PROBE = os.path.join(HERE, "..", "tools", "probes", "random_rows_probe")
+
+
+def build_row_probe(force: bool = False) -> str:
+    """tools/probes/random_rows_probe.cu: the random-row rate of HBM that bench.py quotes beside the gather kernel's."""
+    src = ROW_PROBE + ".cu"
+    if not os.path.exists(src):
+        return ""
+    if force or _stale(ROW_PROBE, [src]):
+        subprocess.check_call([_nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-o", ROW_PROBE, src])
+    return ROW_PROBE
+
+
 def build_all(force: bool = False) -> None:
     build_library(force)
     build_host_demo(force)
     build_stream_sweep(force)
+    build_row_probe(force)
