@@ -8,5 +8,5 @@ bench.write_model("/tmp/wd_sweep.ctrw", 1 << 22)
 PY
 for g in $GS; do
   echo "== $g GPU(s)"
-  timeout 900 ./distributed-tf-serving_b200/stream_sweep_host --lib distributed-tf-serving_b200/libctr_b200.so --weights /tmp/wd_sweep.ctrw --devices $g --out gpurun_out/r01_stream_sweep_g$g.md
+  timeout 900 ./distributed-tf-serving_b200/stream_sweep_host --lib distributed-tf-serving_b200/libctr_b200.so --weights /tmp/wd_sweep.ctrw --devices $g --workers ${WORKERS:-12} --out gpurun_out/${TAG:-r02}_stream_sweep_g$g.md
 done
