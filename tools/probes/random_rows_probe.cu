@@ -80,6 +80,30 @@ int main(int argc, char** argv) {
     if (argc > 2) {          // "quick": the one line bench.py reads (128-byte rows, 32 warps per SM, 8 loads in flight per lane)
         return run<8, 8>(table, big, sink, "table >> L2 (HBM)", 4);
     }
+    int n_dev = 0;
+    CK(cudaGetDeviceCount(&n_dev));
+    if (n_dev > 1) {         // the same fetches from a PEER's memory (plain loads over NVLink, what the row-sharded gather does)
+        int can = 0;
+        CK(cudaDeviceCanAccessPeer(&can, 0, 1));
+        if (can) {
+            uint4* remote;
+            const size_t peer_bytes = (size_t)8 << 30;
+            CK(cudaSetDevice(1));
+            CK(cudaMalloc(&remote, peer_bytes));
+            CK(cudaMemset(remote, 1, peer_bytes));
+            CK(cudaDeviceSynchronize());
+            CK(cudaSetDevice(0));
+            CK(cudaDeviceEnablePeerAccess(1, 0));
+            const char* what = "peer table (NVLink)";
+            if (run<4, 8>(remote, peer_bytes, sink, what, 4)) return 1;
+            if (run<8, 2>(remote, peer_bytes, sink, what, 4)) return 1;
+            if (run<8, 8>(remote, peer_bytes, sink, what, 4)) return 1;
+            if (run<8, 8>(remote, peer_bytes, sink, what, 8)) return 1;
+            if (run<8, 16>(remote, peer_bytes, sink, what, 8)) return 1;
+            if (run<16, 8>(remote, peer_bytes, sink, what, 8)) return 1;
+            if (run<32, 8>(remote, peer_bytes, sink, what, 8)) return 1;
+        }
+    }
     for (int pass = 0; pass < 2; ++pass) {
         const size_t bytes = pass == 0 ? big : small;
         const char* what = pass == 0 ? "table >> L2 (HBM)" : "table 48 MB (L2)";
