@@ -11,7 +11,7 @@ LIB = os.path.join(HERE, "libctr_b200.so")
 HOST_DEMO = os.path.join(HERE, "dcn_client_host")
 STREAM_SWEEP = os.path.join(HERE, "stream_sweep_host")
 SOURCES = ["engine.cu", "engine_base.cuh", "weight_file.cuh", "engine_state.cuh", "device_setup.cuh", "device_path.cuh", "workers.cuh",
-           "debug_hooks.cuh", "static_scratch.cuh", "exchange.cuh", "exchange_host.cuh", "common.cuh", "gather.cuh", "tower.cuh", "sort.cuh", "wire.hpp",
+           "sm_split.cuh", "debug_hooks.cuh", "static_scratch.cuh", "exchange.cuh", "exchange_host.cuh", "common.cuh", "gather.cuh", "tower.cuh", "sort.cuh", "wire.hpp",
            os.path.join("..", "..", "include", "ctr_engine.h")]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

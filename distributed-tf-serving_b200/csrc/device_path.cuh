@@ -116,10 +116,10 @@ void timeline_dump() {
 }
 
 // Records a CUDA event on the launching stream in front of a stage (stage -2 = end of chunk).
-void mark(ctr_engine* e, Slot& s, int stage) {
+void mark(ctr_engine* e, Slot& s, int stage, cudaStream_t on = nullptr) {
     if (!e->timing || !s.time_this || !s.tev || s.sets_recorded >= Slot::kTimeSets || s.cur_mark >= Slot::kTimeMarks) return;
     s.mark_stage[s.cur_mark] = stage;
-    cudaEventRecord(s.tev[s.sets_recorded][s.cur_mark++], s.stream);
+    cudaEventRecord(s.tev[s.sets_recorded][s.cur_mark++], on ? on : s.stream);
     if (stage == -2) { s.n_marks = s.cur_mark; s.cur_mark = 0; ++s.sets_recorded; s.time_this = false; }
 }
 
@@ -127,7 +127,14 @@ void mark(ctr_engine* e, Slot& s, int stage) {
 int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, int n, float* d_scores) {
     const ModelDesc& m = e->m;
     DeviceModel& dm = dc.model;
-    cudaStream_t st = s.stream;
+    // with an SM split the gather goes to the gather's SMs and the chains to the tower's; `s.stream` joins at the end
+    const bool split = dc.split.on && s.g_stream && m.kind != CTR_MODEL_LR;
+    cudaStream_t st = split ? s.g_stream : s.stream;
+    const int gather_sms = split ? dc.split.gather_sms : dm.num_sms, tower_sms = split ? dc.split.tower_sms : dm.num_sms;
+    if (split) {
+        CUDA_TRY(cudaEventRecord(s.ev_in, s.stream));
+        CUDA_TRY(cudaStreamWaitEvent(s.g_stream, s.ev_in, 0));
+    }
     const bool sharded = e->cfg.shard_mode == CTR_TABLES_ROW_SHARDED && e->cfg.n_devices > 1 && !in.table_override;
     const bool compact = !in.reference_layout(m.F);
 
@@ -155,24 +162,31 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
     for (int g = 0; g < CTR_MAX_DEVICES; ++g) gp.shard_base[g] = e->shard_base[g];
     if (m.kind == CTR_MODEL_LR) { gp.scores = d_scores; }
     else { gp.X = s.buf[0]; gp.ldx = s.ld[0]; gp.wide = m.kind == CTR_MODEL_DCN_V2 ? nullptr : s.d_wide; }
-    mark(e, s, 0);
-    const int tl_slot = (int)(reinterpret_cast<uintptr_t>(st) >> 4 & 0xff);
+    mark(e, s, 0, st);
+    const int tl_slot = (int)(reinterpret_cast<uintptr_t>(s.stream) >> 4 & 0xff);
     timeline_mark("gather begin", tl_slot, st);
-    launch_gather(m, compact, gp, n, dm.num_sms, st);
+    launch_gather(m, compact, gp, n, gather_sms, st);
     timeline_mark("gather end", tl_slot, st);
     CUDA_TRY(cudaGetLastError());
     e->launches.fetch_add(1, std::memory_order_relaxed);
+    if (split) {
+        mark(e, s, -3, st);                                    // end of the gather on its own stream (stage -3: not a stage)
+        CUDA_TRY(cudaEventRecord(s.ev_g, s.g_stream));
+        CUDA_TRY(cudaStreamWaitEvent(s.t_stream, s.ev_g, 0));
+        st = s.t_stream;
+        timeline_mark("tower begin", tl_slot, st);
+    }
     int li = 0;
     static const bool chain_prof_env = getenv("CTR_CHAIN_PROF") != nullptr;  // bring-up: in-kernel cycle counters to stderr
     const bool chain_prof = chain_prof_env && s.owns_buffers;                // it allocates: never on the no-allocation path
     for (const Chain& c : s.chains) {
-        mark(e, s, ++li);
+        mark(e, s, ++li, st);
         long long* d_prof = nullptr;
         if (chain_prof) {
             CUDA_TRY(cudaMalloc(&d_prof, (size_t)dm.num_sms * 8 * sizeof(long long)));
             CUDA_TRY(cudaMemsetAsync(d_prof, 0, (size_t)dm.num_sms * 8 * sizeof(long long), st));
         }
-        int32_t rc = launch_chain(c, s, n, d_scores, dm.num_sms, st, d_prof, dc.active.load(std::memory_order_relaxed) > 1);
+        int32_t rc = launch_chain(c, s, n, d_scores, tower_sms, st, d_prof, dc.active.load(std::memory_order_relaxed) > 1);
         if (rc != CTR_OK) { if (d_prof) cudaFree(d_prof); return rc; }
         e->launches.fetch_add(1, std::memory_order_relaxed);
         if (chain_prof) {
@@ -194,7 +208,11 @@ int32_t score_chunk(ctr_engine* e, DeviceCtx& dc, Slot& s, const InputView& in, 
         }
     }
     timeline_mark("tower end", tl_slot, st);
-    mark(e, s, -2);
+    mark(e, s, -2, st);
+    if (split) {
+        CUDA_TRY(cudaEventRecord(s.ev_t, s.t_stream));
+        CUDA_TRY(cudaStreamWaitEvent(s.stream, s.ev_t, 0));
+    }
     return CTR_OK;
 }
 

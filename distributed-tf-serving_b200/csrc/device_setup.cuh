@@ -282,6 +282,9 @@ void free_slot(Slot& s) {
         delete[] s.tev;
     }
     if (s.join_ev) cudaEventDestroy(s.join_ev);
+    if (s.g_stream) cudaStreamDestroy(s.g_stream);
+    if (s.t_stream) cudaStreamDestroy(s.t_stream);
+    for (cudaEvent_t ev : {s.ev_in, s.ev_g, s.ev_t}) if (ev) cudaEventDestroy(ev);
     if (s.stream && s.owns_stream) cudaStreamDestroy(s.stream);
     s = Slot();
 }
@@ -384,6 +387,18 @@ int32_t build_slot_plan(ctr_engine* e, DeviceCtx& dc, Slot& s, bool host_staging
     s.scratch_tiles = ps.n_slices * tiles_in_flight() * 2;      // 128-row tiles in each scratch buffer
     set_scratch_window(dc, s.stream);
     return build_chains(e, dm, s);
+}
+
+// The slot's two streams on the device's SM partitions (no-op without a split).
+int32_t init_slot_split(const SmSplit& split, Slot& s) {
+    if (!split.on) return CTR_OK;
+    int32_t rc;
+    if ((rc = split_stream(split, true, &s.g_stream)) != CTR_OK) return rc;
+    if ((rc = split_stream(split, false, &s.t_stream)) != CTR_OK) return rc;
+    CUDA_TRY(cudaEventCreateWithFlags(&s.ev_in, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&s.ev_g, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventCreateWithFlags(&s.ev_t, cudaEventDisableTiming));
+    return CTR_OK;
 }
 
 int32_t init_slot_common(Slot& s, int dev, cudaStream_t stream /*nullptr -> create*/) {

@@ -44,6 +44,7 @@
 #include "weight_file.cuh"
 #include "exchange.cuh"
 #include "engine_state.cuh"
+#include "sm_split.cuh"
 #include "device_setup.cuh"
 #include "device_path.cuh"
 #include "workers.cuh"
@@ -150,6 +151,11 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
         if ((rc = load_model_on_device(e, i, hw)) != CTR_OK) return rc;
         e->shard_base[i] = e->devs[i]->model.table;
         if ((rc = alloc_pair_scratch(e, *e->devs[i])) != CTR_OK) return rc;
+        if (const char* c = getenv("CTR_SM_SPLIT")) {
+            const int g = atoi(c);
+            if (g >= 8 && g <= e->devs[i]->model.num_sms - 16 && e->m.kind != CTR_MODEL_LR &&
+                (rc = setup_sm_split(e->devs[i]->split, e->cfg.device_ids[i], g)) != CTR_OK) return rc;
+        }
     }
     for (int i = 0; i < e->cfg.n_devices; ++i) {
         DeviceCtx& dc = *e->devs[i];
@@ -158,6 +164,7 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
         for (int w = 0; w < e->cfg.workers_per_device; ++w) {
             std::unique_ptr<Slot> s(new Slot());
             if ((rc = init_slot_common(*s, dev, nullptr)) != CTR_OK) return rc;
+            if ((rc = init_slot_split(dc.split, *s)) != CTR_OK) return rc;
             if ((rc = build_slot_plan(e, dc, *s, true)) != CTR_OK) return rc;
             dc.worker_slots.push_back(std::move(s));
         }
@@ -170,6 +177,7 @@ int32_t ctr_engine_load_weights(ctr_engine* e, const char* path) {
         for (int w = 0; w < n_dev_slots; ++w) {
             std::unique_ptr<Slot> s(new Slot());
             if ((rc = init_slot_common(*s, dev, nullptr)) != CTR_OK) return rc;
+            if ((rc = init_slot_split(dc.split, *s)) != CTR_OK) return rc;
             if ((rc = build_slot_plan(e, dc, *s, false)) != CTR_OK) return rc;
             dc.dev_slots.push_back(std::move(s));
         }

@@ -72,9 +72,20 @@ struct SortBufs {
 };
 
 // One stream with its private activation buffers ("slot"): everything a shard needs on the device.
+// The gather and the tower on disjoint sets of SMs (sm_split.cuh); off unless CTR_SM_SPLIT asks for it.
+struct SmSplit {
+    bool on = false;
+    int gather_sms = 0, tower_sms = 0;
+    CUgreenCtx gather_ctx = nullptr, tower_ctx = nullptr;
+};
+
 struct Slot {
     int dev = -1;
     cudaStream_t stream = nullptr;
+    // SM split: the gather runs on g_stream (the gather's SMs) after ev_in, the chains on t_stream (the tower's SMs)
+    // after ev_g, and `stream` continues after ev_t -- callers of score_chunk still only see `stream`
+    cudaStream_t g_stream = nullptr, t_stream = nullptr;
+    cudaEvent_t ev_in = nullptr, ev_g = nullptr, ev_t = nullptr;
     bool owns_stream = true;
     bool owns_buffers = true;  // false: the buffers are slices of the fixed scratch of ctr_score_device_static
     int64_t cap = 0;           // candidate capacity of the id/weight/score buffers
@@ -139,6 +150,7 @@ struct PairScratch {
 struct DeviceCtx {
     DeviceModel model;
     PairScratch scratch;
+    SmSplit split;
     size_t l2_persist_bytes = 0, l2_window_max = 0;    // persisting-L2 set-aside of the device / largest access window
     std::vector<std::unique_ptr<Slot>> worker_slots;
     std::vector<std::unique_ptr<Slot>> dev_slots;     // for ctr_score_device

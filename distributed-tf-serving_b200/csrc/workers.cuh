@@ -206,6 +206,7 @@ void free_device_state(ctr_engine* e) {
         dc.worker_slots.clear();
         dc.dev_slots.clear();
         free_pair_scratch(dc);
+        free_sm_split(dc.split);
         if (dc.model.dev >= 0) free_model(dc.model);
         if (dc.sort_cap) {
             cudaFree(dc.srt_scores);
