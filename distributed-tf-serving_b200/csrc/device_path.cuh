@@ -84,7 +84,7 @@ int32_t launch_chain(const Chain& c, const Slot& s, int n, float* d_scores, int 
     static const int spread_env = [] { const char* c = getenv("CTR_TOWER_SPREAD"); return c ? (atoi(c) ? 1 : 0) : -1; }();
     const bool spread = spread_env >= 0 ? spread_env == 1 : !busy;
     const int want = (tiles_in_flight() == 2 && !spread) ? (tiles + 1) / 2 : tiles;
-    const int pairs = std::max(1, std::min(std::min(want, num_sms / 2), s.scratch_rows / (2 * kBM)));
+    const int pairs = std::max(1, std::min(std::min(std::min(want, num_sms / 2), s.scratch_rows / (2 * kBM)), tower_pairs_cap()));
     tower_chain_kernel<256><<<2 * pairs, kGemmThreads, ChainCfg<256>::kSmemBytes, st>>>(c.maps, p);
     CUDA_TRY(cudaGetLastError());
     return CTR_OK;

@@ -220,7 +220,7 @@ int32_t alloc_pair_scratch(ctr_engine* e, DeviceCtx& dc) {
     PairScratch& ps = dc.scratch;
     if (m.kind == CTR_MODEL_LR) return CTR_OK;
     CUDA_TRY(cudaSetDevice(dm.dev));
-    ps.n_slices = dm.num_sms / 2;
+    ps.n_slices = std::min(dm.num_sms / 2, tower_pairs_cap());
     const size_t rows = (size_t)ps.n_slices * tiles_in_flight() * 2 * kBM;     // one or two 256-row tiles in flight per slice
     for (int l = 0; l + 1 < (int)dm.mlp.size(); ++l) ps.ld[1 + (l & 1)] = std::max(ps.ld[1 + (l & 1)], dm.mlp[l].Npad);
     if (m.kind == CTR_MODEL_DCN_V2) {

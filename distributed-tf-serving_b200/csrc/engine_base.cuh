@@ -30,6 +30,13 @@ inline int tiles_in_flight() {
     return v;
 }
 
+// CTA pairs a tower launch may use (default: one per TPC).  The tower runs at the power cap, so fewer pairs at a higher
+// clock cost little, and the pair scratch (one slice per pair) shrinks with them.  CTR_TOWER_PAIRS=<n>.
+inline int tower_pairs_cap() {
+    static const int v = [] { const char* c = getenv("CTR_TOWER_PAIRS"); const int n = c ? atoi(c) : 0; return n >= 1 ? n : 1 << 20; }();
+    return v;
+}
+
 // A thread that is about to block on a condition variable first polls for this long: waking a sleeping
 // thread costs 10-20 us on each side of a request whose whole GPU time is ~60 us.  CTR_SPIN_US=0 turns
 // the polling off (hosts with fewer cores than engine threads).

@@ -8,6 +8,10 @@
 // every SM reach it), and the tower loses less than proportionally when it gets fewer SMs (it runs power-capped: 66 of
 // 74 pairs cost 5 %).  A green context is CUDA's way to give a stream a fixed set of SMs.
 //
+// Measured (profiles/r02_split_sweep.txt): best split 48 / 100 SMs, 305 M candidates/s against 321-326 M
+// for one kernel after the other -- the gather needs ~60 SMs for its full rate and the tower pays for what it gives up -- so
+// this stays off by default.
+//
 // CTR_SM_SPLIT=<SMs for the gather> switches it on (a multiple of 8; the tower gets the rest).  Driver entry points
 // come from cudaGetDriverEntryPoint: the library does not link libcuda.
 #pragma once
