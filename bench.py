@@ -495,7 +495,7 @@ def main():
                "d2h_bytes_per_step": int(d2h_step), "ms_per_step": t_e2e / args.steps * 1e3,
                "caller_bytes_per_step": n * F * 12, "h2d_gbs_per_gpu": h2d_step * args.steps / t_e2e / 1e9,
                "how": "R ctr_predict_async + ctr_wait per step from pinned host buffers (the reference's layout: int64 id + float weight per "
-                      "field slot, 468 B per candidate); %d worker streams per GPU; with 8 or more shards in flight the workers narrow their "
+                      "field slot, 468 B per candidate); %d worker streams per GPU; with 5 or more shards in flight the workers narrow their "
                       "shard on the host before it crosses the link (ctr_config.host_pack = 0)" % args.workers}
         assert np.array_equal(pin_o.array[:C], d_out[:C].cpu().numpy()), "host path and device path disagree"
         # request latency (reference window DC:141 -> DC:198 without the sort): one 10k request at a time

@@ -36,7 +36,11 @@ void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t st
 // slot): rows[n, F] uint32 + weights[n, Wk] of the fields in `mask`, written behind each other into `slab`.  The loops are
 // plain and branch-free so that the compiler vectorises them.  Returns the fields that carry a weight != 1.0 but are not
 // in `mask` (the caller adds them and packs again); *wide is set when some id does not fit 32 bits.
-constexpr int kNarrowWhenActive = 8;
+constexpr int kNarrowWhenActive = 5;
+inline int narrow_when_active() {            // CTR_NARROW_AT=<shards in flight on the GPU from which a worker narrows its shard>
+    static const int v = [] { const char* c = getenv("CTR_NARROW_AT"); const int n = c ? atoi(c) : 0; return n >= 1 ? n : kNarrowWhenActive; }();
+    return v;
+}
 
 uint64_t narrow_reference(const int64_t* ids, const float* wts, int64_t n, int F, uint64_t mask, uint32_t* rows, float* pw, bool* wide) {
     int wf[CTR_MAX_FIELDS], Wk = 0;
@@ -70,12 +74,15 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
         // Host narrowing (ctr_config.host_pack): a reference-layout shard for a direct-id table becomes uint32 rows +
         // the weights of the fields that ever had one, packed into this slot's pinned slab -- 208 instead of 468 bytes
         // per candidate for the Criteo shape, the same kernels and the same bits as ctr_predict_packed_async.  A core
-        // narrows at ~10 GB/s of input (measured: 0.45 ms per 10 000 candidates), the link moves 48 GB/s shared by the
-        // shards in flight: narrowing wins from about 8 concurrent shards on (6 workers: 103 -> 89 M candidates/s end
-        // to end, 12 workers: 103 -> 145 M), so that is where the automatic mode switches it on.
+        // narrows ~9.5 GB/s of input (0.49 ms per 10 000 candidates, bound by its own DRAM read rate), the link moves
+        // 41-48 GB/s shared by the shards in flight.  Measured end to end on one GPU (profiles/r02_narrow_sweep.txt):
+        // 3 workers saturate the link at 103 M candidates/s and narrowing their shards gives 62 M, so few shards in flight
+        // travel as they are; 12 workers: 103 M never narrowing, 164-174 M always, 179-181 M from 5 shards in flight on
+        // (173-175 M from 8), which is the automatic mode.  A rule driven by a clock of the copies queued on the link was
+        // tried as well and mixed worse at 12 workers (143-157 M), better at 6 (121-127 against 103-111 M).
         const int hp = e->host_pack;
         if (in.reference_layout(e->m.F) && e->m.id_mode == CTR_ID_DIRECT && hp != 1 && t.n > 0 &&
-            (hp == 2 || dc.active.load(std::memory_order_relaxed) >= kNarrowWhenActive)) {
+            (hp == 2 || dc.active.load(std::memory_order_relaxed) >= narrow_when_active())) {
             const int F = e->m.F;
             uint32_t* rows = reinterpret_cast<uint32_t*>(s.h_ids);
             float* pw = reinterpret_cast<float*>(rows + (size_t)t.n * F);

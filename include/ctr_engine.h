@@ -76,8 +76,8 @@ typedef struct ctr_config {
                                    * uint32 rows + weights only for the fields that ever had one != 1.0 (the packed layout of
                                    * ctr_predict_packed_async, 208 instead of 468 bytes per candidate for the Criteo shape;
                                    * direct-id tables only; same scores, bit for bit).  It trades host CPU (~0.45 ms of one core
-                                   * per 10 000 candidates) for link capacity: 0 = when 8 or more shards are in flight on the GPU
-                                   * (needs workers_per_device >= 8; fewer shards share the link faster than a core narrows),
+                                   * per 10 000 candidates) for link capacity: 0 = when 5 or more shards are in flight on the GPU
+                                   * (needs workers_per_device >= 5; fewer shards share the link faster than a core narrows),
                                    * 1 = never, 2 = always */
     int32_t reserved[6];
 } ctr_config;
