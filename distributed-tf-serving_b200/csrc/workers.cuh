@@ -37,6 +37,7 @@ void complete_shard(ctr_engine* e, const std::shared_ptr<Request>& r, int32_t st
 // plain and branch-free so that the compiler vectorises them.  Returns the fields that carry a weight != 1.0 but are not
 // in `mask` (the caller adds them and packs again); *wide is set when some id does not fit 32 bits.
 constexpr int kNarrowWhenActive = 5;
+constexpr int kNarrowMinWorkers = 8;         // the automatic mode needs this many worker threads (and so cores) on the GPU
 inline int narrow_when_active() {            // CTR_NARROW_AT=<shards in flight on the GPU from which a worker narrows its shard>
     static const int v = [] { const char* c = getenv("CTR_NARROW_AT"); const int n = c ? atoi(c) : 0; return n >= 1 ? n : kNarrowWhenActive; }();
     return v;
@@ -79,10 +80,12 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
         // 3 workers saturate the link at 103 M candidates/s and narrowing their shards gives 62 M, so few shards in flight
         // travel as they are; 12 workers: 103 M never narrowing, 164-174 M always, 179-181 M from 5 shards in flight on
         // (173-175 M from 8), which is the automatic mode.  A rule driven by a clock of the copies queued on the link was
-        // tried as well and mixed worse at 12 workers (143-157 M), better at 6 (121-127 against 103-111 M).
+        // tried as well and mixed worse at 12 workers (143-157 M), better at 6 (121-127 against 103-111 M).  The cores have
+        // to be there: 4 GPUs with 7 workers each on a 32-core host lose with it (284 against 396 M: all the workers narrow
+        // at once and the host's memory cannot feed them), so the automatic mode also wants 8 or more workers on the GPU.
         const int hp = e->host_pack;
         if (in.reference_layout(e->m.F) && e->m.id_mode == CTR_ID_DIRECT && hp != 1 && t.n > 0 &&
-            (hp == 2 || dc.active.load(std::memory_order_relaxed) >= narrow_when_active())) {
+            (hp == 2 || (e->cfg.workers_per_device >= kNarrowMinWorkers && dc.active.load(std::memory_order_relaxed) >= narrow_when_active()))) {
             const int F = e->m.F;
             uint32_t* rows = reinterpret_cast<uint32_t*>(s.h_ids);
             float* pw = reinterpret_cast<float*>(rows + (size_t)t.n * F);

@@ -77,7 +77,8 @@ typedef struct ctr_config {
                                    * ctr_predict_packed_async, 208 instead of 468 bytes per candidate for the Criteo shape;
                                    * direct-id tables only; same scores, bit for bit).  It trades host CPU (~0.45 ms of one core
                                    * per 10 000 candidates) for link capacity: 0 = when 5 or more shards are in flight on the GPU
-                                   * (needs workers_per_device >= 5; fewer shards share the link faster than a core narrows),
+                                   * and workers_per_device >= 8 (fewer shards share the link faster than a core narrows, and
+                                   * the cores have to be there: budget ~10 per GPU, else set 1),
                                    * 1 = never, 2 = always */
     int32_t reserved[6];
 } ctr_config;
