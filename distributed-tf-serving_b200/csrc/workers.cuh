@@ -82,7 +82,8 @@ void run_task(ctr_engine* e, DeviceCtx& dc, Slot& s, const Task& t) {
         // (173-175 M from 8), which is the automatic mode.  A rule driven by a clock of the copies queued on the link was
         // tried as well and mixed worse at 12 workers (143-157 M), better at 6 (121-127 against 103-111 M).  The cores have
         // to be there: 4 GPUs with 7 workers each on a 32-core host lose with it (284 against 396 M: all the workers narrow
-        // at once and the host's memory cannot feed them), so the automatic mode also wants 8 or more workers on the GPU.
+        // at once and the host's memory cannot feed them; narrowing only the shards that find the link busy gives 360 M there),
+        // so the automatic mode also wants 8 or more workers on the GPU.
         const int hp = e->host_pack;
         if (in.reference_layout(e->m.F) && e->m.id_mode == CTR_ID_DIRECT && hp != 1 && t.n > 0 &&
             (hp == 2 || (e->cfg.workers_per_device >= kNarrowMinWorkers && dc.active.load(std::memory_order_relaxed) >= narrow_when_active()))) {
